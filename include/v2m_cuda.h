@@ -1,0 +1,174 @@
+/*
+ * v2m_cuda.h — C ABI of libv2m_cuda.so, the B200 (sm_100a) implementation of vcf2multialign's
+ * aligned-sequence materialisation path.
+ *
+ * The reference is a C++ static library (libvcf2multialign.a) without any FFI; "drop-in" means link-time
+ * substitution of the symbols listed below. Each entry point cites the reference interface it stands behind
+ * (paths relative to the reference checkout). The C++ adapters that re-create those interfaces on top of this
+ * ABI live in vcf2multialign_b200/host/ (see INTEGRATION.md).
+ *
+ * Conventions: every call returns 0 on success and a non-zero status otherwise; v2m_cuda_last_error() returns
+ * the message of the calling thread's last failure. Plain pointers and sizes only. There is no CPU fallback:
+ * without a CUDA device every compute call fails with V2M_ERR_CUDA.
+ *
+ * Bit-matrix layout (libbio int_matrix, lib/libbio/include/libbio/int_matrix/int_matrix.hh:144-175,
+ * int_vector/int_vector.hh:253-261): column-major, element (y, x) is bit ((x*rows + y) % 64) of
+ * 64-bit word ((x*rows + y) / 64); rows and cols are multiples of 64 for every matrix passed here.
+ */
+#ifndef V2M_CUDA_H
+#define V2M_CUDA_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define V2M_OK            0
+#define V2M_ERR_ARGUMENT  1
+#define V2M_ERR_CUDA      2
+#define V2M_ERR_STATE     3
+
+/* variant_graph::PLOIDY_MAX (include/vcf2multialign/variant_graph.hh:55): "follow REF edges only". */
+#define V2M_PLOIDY_MAX 0xffffffffu
+
+typedef struct v2m_graph_s *v2m_graph_t;   /* device-resident variant graph + reference */
+typedef struct v2m_plan_s *v2m_plan_t;     /* a set of output rows (haplotypes or founders) resolved on device */
+
+/* Flat view of v2m::variant_graph (include/vcf2multialign/variant_graph.hh:57-66) + the reference sequence
+ * (sequence_type, variant_graph.hh:33). std::vector<std::string> alt_edge_labels is flattened into offsets + chars. */
+typedef struct v2m_graph_view
+{
+	uint64_t        node_count;                    /* reference_positions.size() */
+	uint64_t        edge_count;                    /* alt_edge_targets.size() */
+	const uint64_t *reference_positions;           /* [node_count] */
+	const uint64_t *aligned_positions;             /* [node_count] */
+	const uint64_t *alt_edge_targets;              /* [edge_count] */
+	const uint64_t *alt_edge_count_csum;           /* [node_count + 1] */
+	const uint64_t *label_offsets;                 /* [edge_count + 1] into label_chars */
+	const char     *label_chars;
+	/* paths_by_edge_and_chrom_copy: rows = h_pad chromosome copies, cols = e_pad edges (edge-major lines).
+	 * paths_by_chrom_copy_and_edge: rows = e_pad, cols = h_pad (copy-major lines); may be NULL, in which case it is
+	 * produced on the device with the K1 transpose, as variant_graph.cc:453 does on the host. */
+	const uint64_t *paths_by_edge_and_chrom_copy;
+	const uint64_t *paths_by_chrom_copy_and_edge;
+	uint64_t        h_pad;
+	uint64_t        e_pad;
+	uint32_t        total_chromosome_copies;       /* ploidy_csum.back() */
+	const char     *ref_seq;
+	uint64_t        ref_len;
+	/* Non-zero: the two path pointers above are DEVICE pointers (e.g. filled by v2m_cuda_synth_paths or by an upstream
+	 * kernel); they are copied device-to-device. */
+	int             paths_on_device;
+} v2m_graph_view;
+
+/* --- library / device ------------------------------------------------------------------------------------ */
+const char *v2m_cuda_last_error(void);
+int v2m_cuda_init(int device);                      /* cudaSetDevice + context warm-up */
+int v2m_cuda_device_count(int *count);
+/* Counts of kernels this library has launched since load (for bench.py's gpu_launches). */
+uint64_t v2m_cuda_launch_count(void);
+
+/* Pinned host / device buffers and plain copies, so that callers (tests, bench, host adapters) need no CUDA headers. */
+void *v2m_cuda_host_alloc(uint64_t bytes);
+void v2m_cuda_host_free(void *p);
+void *v2m_cuda_device_alloc(uint64_t bytes);
+void v2m_cuda_device_free(void *p);
+int v2m_cuda_memcpy_d2h(void *dst, const void *d_src, uint64_t bytes);
+int v2m_cuda_memcpy_h2d(void *d_dst, const void *src, uint64_t bytes);
+int v2m_cuda_synchronize(void);
+/* CUDA events on the library's launching stream (NULL = default stream). */
+void *v2m_cuda_event_create(void);
+void v2m_cuda_event_destroy(void *ev);
+int v2m_cuda_event_record(void *ev, void *stream);
+int v2m_cuda_event_elapsed_ms(void *e0, void *e1, float *ms);   /* synchronises on e1 */
+
+/* --- K1: v2m::transpose_matrix (include/vcf2multialign/transpose_matrix.hh:14,
+ *         libvcf2multialign/transpose_matrix.cc:41-109) ---------------------------------------------------- */
+/* Host buffers; dst has the same word count as src. rows, cols multiples of 64 (else V2M_ERR_ARGUMENT, the
+ * reference asserts); cols == 0 is a no-op (the reference returns a default matrix). */
+int v2m_cuda_transpose_bits(const uint64_t *src, uint64_t rows, uint64_t cols, uint64_t *dst);
+/* Device buffers, asynchronous on `stream` (a cudaStream_t cast to void*; NULL = default stream). */
+int v2m_cuda_transpose_bits_device(const void *d_src, uint64_t rows, uint64_t cols, void *d_dst, void *stream);
+
+/* --- graph residency ------------------------------------------------------------------------------------- */
+int v2m_cuda_graph_upload(const v2m_graph_view *view, v2m_graph_t *out);
+int v2m_cuda_graph_free(v2m_graph_t g);
+int v2m_cuda_graph_aligned_length(v2m_graph_t g, uint64_t *out);   /* aligned_positions.back() */
+/* Copy-major path words as resident on the device (rows = e_pad, cols = h_pad): lets callers fetch the K1 result
+ * when the view did not supply paths_by_chrom_copy_and_edge. */
+int v2m_cuda_graph_download_paths_by_chrom_copy_and_edge(v2m_graph_t g, uint64_t *dst);
+/* The REF-aligned template (= the bytes of the REF row), A bytes. */
+int v2m_cuda_graph_download_template(v2m_graph_t g, uint8_t *dst);
+
+/* --- K2a: which ALT edges each output row follows
+ *          (the edge test + jump in v2m::output_sequence, libvcf2multialign/sequence_writer.cc:44-67) ------ */
+/* Haplotype rows: row i follows chromosome copy copy_idx[i] (sequence_writing_delegate::chromosome_copy_index,
+ * include/vcf2multialign/sequence_writer.hh:16-36; haplotype_output.cc:22-32). V2M_PLOIDY_MAX = the REF row. */
+int v2m_cuda_plan_haplotypes(v2m_graph_t g, const uint32_t *copy_idx, uint32_t n_rows, v2m_plan_t *out);
+/* Founder rows: row f switches to chromosome copy assigned[f*n_segments + s] at node cut_positions[s]
+ * (founder_sequence_writing_delegate, libvcf2multialign/founder_sequence_greedy_output.cc:78-115; `assigned` is the
+ * column-major lb::matrix of founder_sequence_greedy_output::assigned_samples(), segments × founders).
+ * cut_positions has n_segments + 1 node ids, first 0, last the sink. */
+int v2m_cuda_plan_founders(v2m_graph_t g, const uint64_t *cut_positions, uint64_t n_segments,
+                           const uint32_t *assigned, uint32_t n_founders, v2m_plan_t *out);
+int v2m_cuda_plan_free(v2m_plan_t p);
+int v2m_cuda_plan_row_count(v2m_plan_t p, uint32_t *out);
+/* Taken-edge bits, one line of e_pad bits per row (bit e set iff the row's walk follows ALT edge e). */
+int v2m_cuda_plan_download_taken(v2m_plan_t p, uint64_t *dst);
+/* Per-row output length: aligned → A for every row; unaligned → Σ piece lengths (sequence_writer.cc:80). */
+int v2m_cuda_plan_row_lengths(v2m_plan_t p, int unaligned, uint64_t *out /* [n_rows] */);
+
+/* --- K2b: the bytes of v2m::output_sequence (libvcf2multialign/sequence_writer.cc:70-83) ------------------- */
+/* Aligned rows [row_begin, row_end) × columns [col_begin, col_end) of the plan, sequence bytes only (no FASTA
+ * header, no newline): out[(r - row_begin) * pitch + (c - col_begin)].
+ * Device variant: d_out must be 16-byte aligned, pitch % 16 == 0, col_begin % 16 == 0; asynchronous on `stream`. */
+int v2m_cuda_emit_rows_device(v2m_plan_t p, uint32_t row_begin, uint32_t row_end, uint64_t col_begin, uint64_t col_end,
+                              void *d_out, uint64_t pitch, void *stream);
+/* Host variant: kernels fill device tiles that are copied into `out` (any host memory; pinned is faster). */
+int v2m_cuda_emit_rows(v2m_plan_t p, uint32_t row_begin, uint32_t row_end, uint64_t col_begin, uint64_t col_end,
+                       uint8_t *out, uint64_t pitch);
+/* Unaligned rows (--unaligned: no gap fill): row r is written at out + offsets[r - row_begin], length from
+ * v2m_cuda_plan_row_lengths(…, 1, …). */
+int v2m_cuda_emit_rows_unaligned(v2m_plan_t p, uint32_t row_begin, uint32_t row_end, const uint64_t *offsets, uint8_t *out);
+
+/* --- whole-stream drivers: haplotype_output::output_a2m / founder_sequence_greedy_output::output_a2m
+ *     (libvcf2multialign/haplotype_output.cc:38-82, founder_sequence_greedy_output.cc:515-550) -------------- */
+/* Writes, for every row i of the plan, '>' ids[i] '\n' row-bytes '\n' to file descriptor fd, in row order, streaming
+ * through pinned double buffers. ids: n_rows NUL-terminated strings, concatenated. row_done (may be NULL) is called
+ * from the calling thread after each row has been handed to write(2) — the hook behind output_delegate::handled_sequences. */
+typedef void (*v2m_row_callback)(uint32_t row, void *ctx);
+int v2m_cuda_write_a2m(v2m_plan_t p, const char *ids, int unaligned, int fd, v2m_row_callback row_done, void *ctx);
+
+/* --- K3: per-cut haplotype classes for founder_sequence_greedy_output::find_matchings
+ *         (libvcf2multialign/founder_sequence_greedy_output.cc:213-253, 460-469; pbwt.hh:77-134) ----------- */
+/* For each cut c in 1 … n_cuts-1 (cut_positions[0] == 0), with segment edges [s, e) between cut c-1 and cut c:
+ *   rhs_eq[(c-1)*H + h]   representative of h's class on [s, e) (the member first in the pBWT order at s)
+ *   distinct[c-1]         number of classes                    (rhs_distinct_eq_classes)
+ *   first_class[c-1]      permutation.front() at the cut       (rhs_first_path_eq_class)
+ *   first_is_ref[c-1]     rhs_first_path_is_ref accumulated over [s, e)
+ *   joined triples (lhs_rep, rhs_rep, size) in permutation order for c ≥ 2: joined_offsets[c-1] … joined_offsets[c]
+ *   index into joined (capacity joined_cap triples; V2M_ERR_ARGUMENT if too small, needed count in joined_offsets[n_cuts-1]).
+ */
+int v2m_cuda_segment_classes(v2m_graph_t g, const uint64_t *cut_positions, uint64_t n_cuts,
+                             uint32_t *rhs_eq, uint32_t *distinct, uint32_t *first_class, uint8_t *first_is_ref,
+                             uint64_t *joined_offsets /* [n_cuts] */, uint32_t *joined, uint64_t joined_cap);
+
+/* --- synthetic workloads (measurement infrastructure) ------------------------------------------------ */
+/* Fills d_dst (device, e_pad × h_pad/64 words = paths_by_edge_and_chrom_copy) with LD-structured path bits that are a
+ * pure function of (seed, chromosome copy, site); per edge: its site, its 0-based ALT number, the site's ALT count. */
+int v2m_cuda_synth_paths(void *d_dst, uint64_t h_pad, uint64_t e_pad, uint32_t H, uint64_t E, uint32_t seed,
+                         const uint32_t *edge_site, const uint8_t *edge_alt, const uint8_t *edge_nalts);
+
+/* --- measurement hooks (bench.py) ------------------------------------------------------------------------- */
+/* Mean device time in milliseconds of `iters` back-to-back launches of the named stage on resident data,
+ * measured with CUDA events on the launching stream. */
+int v2m_cuda_time_emit_rows(v2m_plan_t p, uint32_t row_begin, uint32_t row_end, void *d_out, uint64_t pitch,
+                            int iters, float *ms_mean);
+int v2m_cuda_time_transpose_bits(const void *d_src, uint64_t rows, uint64_t cols, void *d_dst, int iters, float *ms_mean);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* V2M_CUDA_H */

@@ -1126,7 +1126,6 @@ struct founder_sequence_greedy_output final : output_base
 		u32 lhs_first_class(0), rhs_first_class(0);
 		std::size_t cut_it(1);
 		pbwt_context pbwt(H);
-		pbwt_context::div_less const lt;
 		u64 const colw(graph.paths_by_edge_and_chrom_copy.number_of_rows() / 64);
 		u64 cut_pos_idx(0);
 
@@ -1149,11 +1148,13 @@ struct founder_sequence_greedy_output final : output_base
 				{
 					u32 const aa(pbwt.permutation[i]);
 					u64 const dd(pbwt.divergence[i]);
-					if (lt(prev_cut_edge_idx, dd)) { rep = aa; ++rhs_distinct; }
+					// u64 < divergence_value resolves to the built-in comparison through the implicit conversion
+					// (pbwt.hh:46), not to divergence_value::operator<, so DIVERGENCE_MAX compares greatest here.
+					if (prev_cut_edge_idx < dd) { rep = aa; ++rhs_distinct; }
 					rhs_eq[aa] = rep;
 					if (0 < cut_pos_idx)
 					{
-						if (lt(cut_pair_edge_idx, dd)) joined.push_back({lhs_eq[aa], rep, 0});
+						if (cut_pair_edge_idx < dd) joined.push_back({lhs_eq[aa], rep, 0});
 						ORACLE_ASSERT(!joined.empty());
 						++joined.back().size;
 					}
@@ -1190,7 +1191,7 @@ struct founder_sequence_greedy_output final : output_base
 			for (u32 i(0); i < H; ++i)
 			{
 				u32 const aa(pbwt.permutation[i]);
-				if (lt(0, pbwt.divergence[i])) { rep = aa; ++rhs_distinct; joined.push_back({PLOIDY_MAX, rep, 0}); }
+				if (0 < pbwt.divergence[i]) { rep = aa; ++rhs_distinct; joined.push_back({PLOIDY_MAX, rep, 0}); }
 				rhs_eq[aa] = rep;
 				ORACLE_ASSERT(!joined.empty());
 				++joined.back().size;

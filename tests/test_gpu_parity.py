@@ -1,0 +1,241 @@
+"""GPU parity tests: the CUDA path (through the C ABI of libv2m_cuda.so) against the CPU oracle, byte for byte."""
+import os
+
+import numpy as np
+import pytest
+
+from oracle import oracle as orc
+from tests import randgraph as rg
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def v2m():
+    import vcf2multialign_b200 as v
+    v._lib.check(v.lib().v2m_cuda_init(0))
+    return v
+
+
+def _set_bit(words, rows, y, x):
+    i = x * rows + y
+    words[i // 64] |= np.uint64(1) << np.uint64(i % 64)
+
+
+def _device_graph(v2m, og, with_ce=False):
+    a = dict(og.arrays())
+    if not with_ce:
+        a["paths_ce"] = None            # let K1 derive it on the device, as variant_graph.cc:453 does on the host
+    g = v2m.VariantGraph.from_arrays(a)
+    return v2m.DeviceGraph(g, og.arrays()["ref"]), g
+
+
+# ---- K1 ------------------------------------------------------------------------------------------------------
+def test_transpose_known_answers(v2m, expected):
+    for kat in expected["transpose_kat"]:
+        rows, cols = kat["rows"], kat["cols"]
+        y, x = kat["set"]
+        src = np.zeros(rows * cols // 64, np.uint64)
+        exp = np.zeros(rows * cols // 64, np.uint64)
+        _set_bit(src, rows, y, x)
+        _set_bit(exp, cols, x, y)
+        assert np.array_equal(v2m.transpose_matrix(src, rows, cols), exp)
+
+
+@pytest.mark.parametrize("seed", range(10))
+def test_transpose_property_vs_oracle(v2m, seed):
+    """tests/transpose_matrix.cc:254-279 (random word dims, a third of the bits set), checked against the oracle."""
+    rng = np.random.default_rng(seed)
+    h, w = (int(x) for x in rng.integers(1, 12, 2))
+    rows, cols = 64 * h, 64 * w
+    src = rng.integers(0, 2**63, rows * cols // 64, dtype=np.uint64) & rng.integers(0, 2**63, rows * cols // 64, dtype=np.uint64)
+    got = v2m.transpose_matrix(src, rows, cols)
+    assert np.array_equal(got, orc.transpose(src, rows, cols))
+    assert np.array_equal(v2m.transpose_matrix(got, cols, rows), src)
+
+
+@pytest.mark.parametrize("rows,cols", [(64, 64), (64, 4096), (4096, 64), (5056, 2112), (1088, 1600), (960, 576), (2112, 5056)])
+def test_transpose_tile_edges(v2m, rows, cols):
+    """Shapes around the 512-line × 1024-row tile borders, incl. the c2/c4 row count (5056 = 4·1024 + 960)."""
+    rng = np.random.default_rng(rows * 7 + cols)
+    src = rng.integers(0, 2**64 - 1, rows * cols // 64, dtype=np.uint64)
+    got = v2m.transpose_matrix(src, rows, cols)
+    assert np.array_equal(got, orc.transpose(src, rows, cols))
+
+
+def test_transpose_large_involution(v2m):
+    """Bigger than the oracle finishes quickly: T(T(x)) == x plus population count and a sampled bit check."""
+    rows, cols = 5056, 64 * 3000
+    rng = np.random.default_rng(5)
+    src = rng.integers(0, 2**64 - 1, rows * cols // 64, dtype=np.uint64) & rng.integers(0, 2**64 - 1, rows * cols // 64, dtype=np.uint64)
+    t = v2m.transpose_matrix(src, rows, cols)
+    assert np.array_equal(v2m.transpose_matrix(t, cols, rows), src)
+    ys, xs = rng.integers(0, rows, 5000), rng.integers(0, cols, 5000)
+    si = xs * rows + ys
+    ti = ys * cols + xs
+    assert np.array_equal((src[si // 64] >> (si % 64).astype(np.uint64)) & 1, (t[ti // 64] >> (ti % 64).astype(np.uint64)) & 1)
+
+
+def test_transpose_rejects_bad_dims(v2m):
+    with pytest.raises(v2m.V2MError):
+        v2m.transpose_matrix(np.zeros(3, np.uint64), 96, 2)
+    assert v2m.transpose_matrix(np.zeros(0, np.uint64), 64, 0).size == 0
+
+
+# ---- K2 on the reference's fixtures ------------------------------------------------------------------------------
+def test_rows_on_reference_fixtures(v2m, expected, golden_dir):
+    for sub, key in (("variant-graph", "variant_graph"), ("founder-sequences", "founder_sequences")):
+        for case in expected[key]:
+            d = os.path.join(golden_dir, sub)
+            og = orc.Graph.from_files(os.path.join(d, case["fa"]), os.path.join(d, case["vcf"]), "1")
+            dg, g = _device_graph(v2m, og)
+            a = og.arrays()
+            assert np.array_equal(dg.paths_by_chrom_copy_and_edge(), a["paths_ce"])
+            assert dg.template() == og.output_sequence(orc.PLOIDY_MAX)
+            H = a["total_copies"]
+            plan = dg.plan_haplotypes([orc.PLOIDY_MAX] + list(range(H)))
+            rows = plan.emit_rows()
+            assert rows[0].tobytes() == og.output_sequence(orc.PLOIDY_MAX)
+            for h in range(H):
+                assert rows[1 + h].tobytes() == og.output_sequence(h), (case["vcf"], h)
+
+
+def test_founder_rows_on_reference_goldens(v2m, expected, golden_dir):
+    """Exact A2M text of tests/founder_sequences.cc:118-188 from the GPU row writer, given the golden cuts and matchings."""
+    for case in expected["founder_sequences"]:
+        d = os.path.join(golden_dir, "founder-sequences")
+        og = orc.Graph.from_files(os.path.join(d, case["fa"]), os.path.join(d, case["vcf"]), "1")
+        dg, g = _device_graph(v2m, og)
+        assigned = np.array(case["assigned_colmajor"], np.uint32).reshape(-1, case["rows"]).T
+        plan = dg.plan_founders(case["cuts"], assigned)
+        rows = plan.emit_rows()
+        text = b">REF\n" + dg.template() + b"\n"
+        for f in range(rows.shape[0]):
+            text += b">" + str(1 + f).encode() + b"\n" + rows[f].tobytes() + b"\n"
+        assert text.decode() == case["a2m"], case["vcf"]
+
+
+# ---- K2 on random graphs -------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("seed", range(24))
+def test_rows_random_graphs(v2m, tmp_path, seed):
+    og = rg.random_oracle_graph(str(tmp_path), seed, ref_len=300 + 211 * seed, n_records=20 + 9 * seed, n_samples=3 + seed % 5,
+                                ploidy=1 + seed % 3, long_del_prob=0.08 if seed % 3 == 0 else 0.0)
+    a = og.arrays()
+    dg, g = _device_graph(v2m, og, with_ce=bool(seed % 2))
+    H = a["total_copies"]
+    plan = dg.plan_haplotypes(list(range(H)) + [orc.PLOIDY_MAX])
+    # K2a: taken-edge bits against the numpy model of the walk
+    taken = plan.taken()
+    for h in range(H):
+        exp = np.zeros(a["e_pad"] // 64, np.uint64)
+        for e in rg.model_taken_edges(a, h):
+            exp[e // 64] |= np.uint64(1) << np.uint64(e % 64)
+        assert np.array_equal(taken[h], exp), (seed, h)
+    assert not taken[H].any()
+    # K2b
+    rows = plan.emit_rows()
+    for h in range(H):
+        assert rows[h].tobytes() == og.output_sequence(h), (seed, h)
+    assert rows[H].tobytes() == og.output_sequence(orc.PLOIDY_MAX)
+
+
+def test_rows_multi_tile_and_column_windows(v2m, tmp_path):
+    """A graph several 4096-column tiles long with long deletions that cross tile borders; arbitrary column windows."""
+    og = rg.random_oracle_graph(str(tmp_path), 1234, ref_len=40000, n_records=2500, n_samples=6, ploidy=2, long_del_prob=0.04)
+    a = og.arrays()
+    dg, g = _device_graph(v2m, og)
+    H = a["total_copies"]
+    A = int(a["aligned_positions"][-1])
+    assert A > 9 * 4096
+    plan = dg.plan_haplotypes(list(range(H)))
+    full = [og.output_sequence(h) for h in range(H)]
+    rows = plan.emit_rows()
+    for h in range(H):
+        assert rows[h].tobytes() == full[h], h
+    rng = np.random.default_rng(0)
+    for _ in range(12):
+        c0, c1 = sorted(int(x) for x in rng.integers(0, A + 1, 2))
+        r0, r1 = sorted(int(x) for x in rng.integers(0, H + 1, 2))
+        win = plan.emit_rows(r0, r1, c0, c1)
+        for i, h in enumerate(range(r0, r1)):
+            assert win[i].tobytes() == full[h][c0:c1], (h, c0, c1)
+
+
+def test_rows_many_rows_blocks(v2m, tmp_path):
+    """More rows than one CTA row block (64) so that blockIdx.y > 0 is exercised, with repeated and REF rows."""
+    og = rg.random_oracle_graph(str(tmp_path), 77, ref_len=9000, n_records=700, n_samples=40, ploidy=2)
+    a = og.arrays()
+    dg, g = _device_graph(v2m, og)
+    H = a["total_copies"]
+    idx = list(range(H)) + [orc.PLOIDY_MAX] + list(range(H - 1, -1, -1)) + [3, 3, orc.PLOIDY_MAX]
+    plan = dg.plan_haplotypes(idx)
+    rows = plan.emit_rows()
+    cache = {}
+    for i, h in enumerate(idx):
+        if h not in cache:
+            cache[h] = og.output_sequence(h)
+        assert rows[i].tobytes() == cache[h], (i, h)
+
+
+def test_founder_rows_random(v2m, tmp_path):
+    """Founder rows given the oracle's cut positions and matchings (K2c = compose + K2a + K2b)."""
+    done = 0
+    for seed in range(30):
+        og = rg.random_oracle_graph(str(tmp_path), 500 + seed, ref_len=600, n_records=60, n_samples=6, ploidy=2, overlap=False, sv=False)
+        f = orc.FounderOutput(og)
+        if not f.find_cut_positions(0):
+            continue
+        try:
+            if not f.find_matchings(3):
+                continue
+        except orc.OracleError:
+            continue    # inputs on which the reference itself asserts / does not terminate (SURVEY §7 hard parts)
+        dg, g = _device_graph(v2m, og)
+        plan = dg.plan_founders(f.cut_positions(), f.assigned_samples())
+        rows = plan.emit_rows()
+        exp = f.output_a2m().split(b"\n")
+        for k in range(rows.shape[0]):
+            assert rows[k].tobytes() == exp[2 * (k + 1) + 1], (seed, k)
+        done += 1
+    assert done >= 10
+
+
+# ---- whole-stream driver ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("chrom,output_ref", [(None, True), ("chr7", True), ("chr7", False)])
+def test_haplotype_output_a2m_stream(v2m, tmp_path, chrom, output_ref):
+    og = rg.random_oracle_graph(str(tmp_path), 4242, ref_len=5000, n_records=400, n_samples=7, ploidy=2)
+    a = og.arrays()
+    g = v2m.VariantGraph.from_arrays(a)
+    events = []
+
+    class delegate(v2m.output_delegate):
+        def will_handle_sample(self, sample, sample_idx, chr_copy_idx): events.append(("will", sample, sample_idx, chr_copy_idx))
+        def handled_sequences(self, n): events.append(("done", n))
+
+    out = v2m.haplotype_output(chrom, output_ref, False, delegate())
+    dst = str(tmp_path / f"out-{chrom}-{output_ref}.a2m")
+    out.output_a2m(a["ref"], g, dst)
+    with open(dst, "rb") as f:
+        got = f.read()
+    assert got == og.haplotype_output_a2m(chrom, output_ref, False)
+    # delegate protocol: seq_count starts at 1 even without the REF row (haplotype_output.cc:46, 78-79)
+    dones = [e[1] for e in events if e[0] == "done"]
+    H = a["total_copies"]
+    assert dones == (list(range(1, H + 2)) if output_ref else list(range(2, H + 2)))
+    assert [e[1:] for e in events if e[0] == "will"] == [(n, s, c) for s, n in enumerate(a["sample_names"]) for c in range(2)]
+    with pytest.raises(FileExistsError):
+        out.output_a2m(a["ref"], g, dst)    # O_CREAT|O_EXCL as lb::open_file_for_writing(CREATE)
+
+
+def test_haplotype_output_separate(v2m, tmp_path):
+    og = rg.random_oracle_graph(str(tmp_path), 99, ref_len=3000, n_records=200, n_samples=4, ploidy=2)
+    a = og.arrays()
+    g = v2m.VariantGraph.from_arrays(a)
+    for include_header in (True, False):
+        d = tmp_path / f"sep{int(include_header)}"
+        d.mkdir()
+        v2m.haplotype_output("c", True, False).output_separate(a["ref"], g, include_header, str(d))
+        exp = og.haplotype_output_separate("c", True, False, include_header)
+        assert sorted(os.listdir(d)) == sorted(n for n, _ in exp)
+        for name, data in exp:
+            assert (d / name).read_bytes() == data, name

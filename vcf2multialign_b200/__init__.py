@@ -1,0 +1,6 @@
+"""vcf2multialign_b200 — B200 (sm_100a) implementation of vcf2multialign's aligned-sequence materialisation path.
+
+Everything here runs through libv2m_cuda.so (include/v2m_cuda.h); there is no CPU fallback."""
+from ._lib import PLOIDY_MAX, V2MError, lib  # noqa: F401
+from .graph import DeviceGraph, Plan, VariantGraph  # noqa: F401
+from .output import haplotype_output, output_delegate, transpose_matrix  # noqa: F401

@@ -1,0 +1,638 @@
+// C ABI of libv2m_cuda.so (include/v2m_cuda.h): graph residency, plans, row emission, transpose.
+// Host-side preparation here is O(N + E) array flattening only; all per-row / per-bit work runs in the kernels.
+#include <algorithm>
+#include <atomic>
+#include <cerrno>
+#include <cstring>
+#include <memory>
+#include <string>
+#include <vector>
+
+#include <unistd.h>
+
+#include "../../include/v2m_cuda.h"
+#include "common.cuh"
+#include "device_graph.hh"
+
+namespace v2m {
+
+	std::string &last_error()
+	{
+		thread_local std::string msg;
+		return msg;
+	}
+
+	int fail(int status, std::string msg)
+	{
+		last_error() = std::move(msg);
+		return status;
+	}
+
+	static std::atomic<u64> g_launches{0};
+	void count_launch(unsigned n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+
+	template <typename T>
+	int dev_alloc(T *&ptr, u64 count)
+	{
+		ptr = nullptr;
+		V2M_CUDA_TRY(cudaMalloc(reinterpret_cast<void **>(&ptr), std::max<u64>(count, 1) * sizeof(T)));
+		return 0;
+	}
+
+	template <typename T>
+	int dev_upload(T *&ptr, T const *src, u64 count, u64 alloc_count = 0, bool src_on_device = false)
+	{
+		alloc_count = std::max(alloc_count, count);
+		if (int const st = dev_alloc(ptr, alloc_count)) return st;
+		if (alloc_count > count)
+			V2M_CUDA_TRY(cudaMemset(ptr + count, 0, (alloc_count - count) * sizeof(T)));
+		if (count)
+			V2M_CUDA_TRY(cudaMemcpy(ptr, src, count * sizeof(T), src_on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice));
+		return 0;
+	}
+
+	struct graph_holder
+	{
+		device_graph		g;
+		std::vector<u64>	csum;	// host copy of alt_edge_count_csum: node id → first edge index
+
+		~graph_holder()
+		{
+			cudaFree(g.ref); cudaFree(g.refpos); cudaFree(g.alnpos); cudaFree(g.edge_src); cudaFree(g.edge_tgt);
+			cudaFree(g.edges); cudaFree(g.label_chars); cudaFree(g.paths_eh); cudaFree(g.paths_he);
+			cudaFree(g.tmpl); cudaFree(g.tile_edges);
+		}
+	};
+
+	struct plan_holder
+	{
+		device_plan				p;
+		graph_holder const		*owner{};
+		std::vector<u64>		unaligned_lengths;
+
+		~plan_holder() { cudaFree(p.taken); }
+	};
+}
+
+using namespace v2m;
+
+struct v2m_graph_s : v2m::graph_holder {};
+struct v2m_plan_s : v2m::plan_holder {};
+
+
+extern "C" {
+
+const char *v2m_cuda_last_error(void) { return last_error().c_str(); }
+
+int v2m_cuda_device_count(int *count)
+{
+	if (!count) return fail(V2M_ERR_ARGUMENT, "count is NULL");
+	V2M_CUDA_TRY(cudaGetDeviceCount(count));
+	return V2M_OK;
+}
+
+int v2m_cuda_init(int device)
+{
+	V2M_CUDA_TRY(cudaSetDevice(device));
+	V2M_CUDA_TRY(cudaFree(nullptr));
+	return V2M_OK;
+}
+
+uint64_t v2m_cuda_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
+
+void *v2m_cuda_host_alloc(uint64_t bytes)
+{
+	void *p(nullptr);
+	if (cudaSuccess != cudaMallocHost(&p, bytes)) { fail(V2M_ERR_CUDA, "cudaMallocHost failed"); return nullptr; }
+	return p;
+}
+
+void v2m_cuda_host_free(void *p) { if (p) cudaFreeHost(p); }
+
+void *v2m_cuda_device_alloc(uint64_t bytes)
+{
+	void *p(nullptr);
+	if (cudaSuccess != cudaMalloc(&p, bytes)) { fail(V2M_ERR_CUDA, "cudaMalloc failed"); return nullptr; }
+	return p;
+}
+
+void v2m_cuda_device_free(void *p) { if (p) cudaFree(p); }
+
+int v2m_cuda_memcpy_d2h(void *dst, const void *d_src, uint64_t bytes)
+{
+	V2M_CUDA_TRY(cudaMemcpy(dst, d_src, bytes, cudaMemcpyDeviceToHost));
+	return V2M_OK;
+}
+
+int v2m_cuda_memcpy_h2d(void *d_dst, const void *src, uint64_t bytes)
+{
+	V2M_CUDA_TRY(cudaMemcpy(d_dst, src, bytes, cudaMemcpyHostToDevice));
+	return V2M_OK;
+}
+
+int v2m_cuda_synchronize(void)
+{
+	V2M_CUDA_TRY(cudaDeviceSynchronize());
+	return V2M_OK;
+}
+
+
+// ---- K1 ---------------------------------------------------------------------------------------------------
+int v2m_cuda_transpose_bits_device(const void *d_src, uint64_t rows, uint64_t cols, void *d_dst, void *stream)
+{
+	if (0 != rows % 64 || 0 != cols % 64)
+		return fail(V2M_ERR_ARGUMENT, "transpose_bits: rows and cols must be multiples of 64 (transpose_matrix.cc:53-54)");
+	if (0 == cols || 0 == rows) return V2M_OK;
+	if (!d_src || !d_dst) return fail(V2M_ERR_ARGUMENT, "transpose_bits: NULL buffer");
+	return launch_transpose_bits(d_src, rows, cols, d_dst, static_cast<cudaStream_t>(stream));
+}
+
+int v2m_cuda_transpose_bits(const uint64_t *src, uint64_t rows, uint64_t cols, uint64_t *dst)
+{
+	if (0 != rows % 64 || 0 != cols % 64)
+		return fail(V2M_ERR_ARGUMENT, "transpose_bits: rows and cols must be multiples of 64 (transpose_matrix.cc:53-54)");
+	if (0 == cols || 0 == rows) return V2M_OK;
+	if (!src || !dst) return fail(V2M_ERR_ARGUMENT, "transpose_bits: NULL buffer");
+	u64 const bytes(rows / 8 * cols);
+	u64 *d_src(nullptr), *d_dst(nullptr);
+	if (int const st = dev_alloc(d_src, bytes / 8)) return st;
+	if (int const st = dev_alloc(d_dst, bytes / 8)) { cudaFree(d_src); return st; }
+	int st(V2M_OK);
+	do
+	{
+		if (cudaSuccess != cudaMemcpy(d_src, src, bytes, cudaMemcpyHostToDevice)) { st = fail(V2M_ERR_CUDA, "H2D copy failed"); break; }
+		if ((st = launch_transpose_bits(d_src, rows, cols, d_dst, nullptr))) break;
+		if (cudaSuccess != cudaMemcpy(dst, d_dst, bytes, cudaMemcpyDeviceToHost)) { st = fail(V2M_ERR_CUDA, "D2H copy failed"); break; }
+	} while (false);
+	cudaFree(d_src); cudaFree(d_dst);
+	return st;
+}
+
+
+// ---- graph ------------------------------------------------------------------------------------------------
+int v2m_cuda_graph_upload(const v2m_graph_view *view, v2m_graph_t *out)
+{
+	if (!view || !out) return fail(V2M_ERR_ARGUMENT, "graph_upload: NULL argument");
+	*out = nullptr;
+	u64 const N(view->node_count), E(view->edge_count);
+	if (N < 1) return fail(V2M_ERR_ARGUMENT, "graph_upload: empty graph");
+	if (!view->reference_positions || !view->aligned_positions || !view->alt_edge_count_csum)
+		return fail(V2M_ERR_ARGUMENT, "graph_upload: NULL node arrays");
+	if (E && (!view->alt_edge_targets || !view->label_offsets))
+		return fail(V2M_ERR_ARGUMENT, "graph_upload: NULL edge arrays");
+	if (0 != view->h_pad % 64 || 0 != view->e_pad % 64 || view->e_pad < E || view->h_pad < view->total_chromosome_copies)
+		return fail(V2M_ERR_ARGUMENT, "graph_upload: path matrix dimensions must be multiples of 64 covering all edges and chromosome copies");
+	if (view->h_pad && view->e_pad && !view->paths_by_edge_and_chrom_copy && !view->paths_by_chrom_copy_and_edge)
+		return fail(V2M_ERR_ARGUMENT, "graph_upload: no path matrix given");
+	u64 const A(view->aligned_positions[N - 1]);
+	if (A >= (u64(1) << 32) - 2 * K2_TCOL || view->ref_len >= (u64(1) << 32))
+		return fail(V2M_ERR_ARGUMENT, "graph_upload: aligned length or reference length does not fit 32-bit device positions");
+	if (view->reference_positions[N - 1] > view->ref_len)
+		return fail(V2M_ERR_ARGUMENT, "graph_upload: node positions exceed the reference length");
+
+	auto holder(std::make_unique<v2m_graph_s>());
+	device_graph &g(holder->g);
+	V2M_CUDA_TRY(cudaGetDevice(&g.device));
+	g.N = N; g.E = E; g.L = view->ref_len; g.A = A;
+	g.h_pad = view->h_pad; g.e_pad = view->e_pad; g.Wh = g.h_pad / 64; g.We = g.e_pad / 64;
+	g.H = view->total_chromosome_copies;
+	g.n_tiles = (A + K2_TCOL - 1) / K2_TCOL;
+	g.A_alloc = std::max<u64>(g.n_tiles, 1) * K2_TCOL;
+	holder->csum.assign(view->alt_edge_count_csum, view->alt_edge_count_csum + N + 1);
+	if (holder->csum[N] != E)
+		return fail(V2M_ERR_ARGUMENT, "graph_upload: alt_edge_count_csum does not match edge_count");
+
+	// Flatten to 32-bit device arrays.
+	std::vector<u32> refpos(N), alnpos(N), edge_src(g.e_pad, 0), edge_tgt(g.e_pad, 0);
+	for (u64 n(0); n < N; ++n)
+	{
+		refpos[n] = u32(view->reference_positions[n]);
+		alnpos[n] = u32(view->aligned_positions[n]);
+		if (n && (view->aligned_positions[n] <= view->aligned_positions[n - 1] || view->reference_positions[n] <= view->reference_positions[n - 1]))
+			return fail(V2M_ERR_ARGUMENT, "graph_upload: node positions must be strictly increasing");
+	}
+	std::vector<edge_rec> edges(g.e_pad, edge_rec{0, 0, 0, 0});
+	for (u64 n(0); n < N; ++n)
+	{
+		u64 const lb(holder->csum[n]), rb(holder->csum[n + 1]);
+		if (lb > rb || rb > E) return fail(V2M_ERR_ARGUMENT, "graph_upload: alt_edge_count_csum is not a cumulative sum");
+		for (u64 e(lb); e < rb; ++e)
+		{
+			u64 const t(view->alt_edge_targets[e]);
+			if (t <= n || t >= N) return fail(V2M_ERR_ARGUMENT, "graph_upload: ALT edge target out of range");
+			u64 const lo(view->label_offsets[e]), hi(view->label_offsets[e + 1]);
+			if (hi < lo || hi - lo > alnpos[t] - alnpos[n])
+				return fail(V2M_ERR_ARGUMENT, "graph_upload: ALT label longer than its aligned span (sequence_writer.cc:61)");
+			if (hi >= (u64(1) << 32)) return fail(V2M_ERR_ARGUMENT, "graph_upload: label store too large");
+			edge_src[e] = u32(n); edge_tgt[e] = u32(t);
+			edges[e] = edge_rec{alnpos[n], alnpos[t], u32(lo), u32(hi - lo)};
+		}
+	}
+	g.label_bytes = E ? view->label_offsets[E] : 0;
+
+	// Per column tile: edges whose span may intersect it.
+	std::vector<uint2> tile_edges(std::max<u64>(g.n_tiles, 1), make_uint2(0, 0));
+	{
+		u64 e_lo(0), e_hi(0), e_back(0);
+		u32 reach(0);			// max a1 over edges [0, e_back]
+		for (u64 b(0); b < g.n_tiles; ++b)
+		{
+			u64 const t0(b * K2_TCOL), t1(t0 + K2_TCOL);
+			while (e_lo < E && edges[e_lo].a0 < t0) ++e_lo;
+			while (e_hi < E && edges[e_hi].a0 < t1) ++e_hi;
+			// first edge whose running maximum of a1 exceeds t0
+			while (e_back < e_lo)
+			{
+				reach = std::max(reach, edges[e_back].a1);
+				if (reach > t0) break;
+				++e_back;
+			}
+			tile_edges[b] = make_uint2(unsigned(std::min(e_back, e_lo)), unsigned(e_hi));
+		}
+	}
+
+	if (int const st = dev_upload(g.ref, reinterpret_cast<u8 const *>(view->ref_seq), g.L, g.L + 16)) return st;
+	if (int const st = dev_upload(g.refpos, refpos.data(), N)) return st;
+	if (int const st = dev_upload(g.alnpos, alnpos.data(), N)) return st;
+	if (int const st = dev_upload(g.edge_src, edge_src.data(), g.e_pad)) return st;
+	if (int const st = dev_upload(g.edge_tgt, edge_tgt.data(), g.e_pad)) return st;
+	if (int const st = dev_upload(g.edges, edges.data(), g.e_pad)) return st;
+	if (int const st = dev_upload(g.label_chars, reinterpret_cast<u8 const *>(view->label_chars), g.label_bytes, g.label_bytes + 16)) return st;
+	if (int const st = dev_upload(g.tile_edges, tile_edges.data(), tile_edges.size())) return st;
+
+	u64 const path_words(g.Wh * g.e_pad);
+	if (path_words)
+	{
+		if (view->paths_by_edge_and_chrom_copy)
+		{
+			if (int const st = dev_upload(g.paths_eh, view->paths_by_edge_and_chrom_copy, path_words, 0, 0 != view->paths_on_device)) return st;
+		}
+		else if (int const st = dev_alloc(g.paths_eh, path_words)) return st;
+
+		if (view->paths_by_chrom_copy_and_edge)
+		{
+			if (int const st = dev_upload(g.paths_he, view->paths_by_chrom_copy_and_edge, path_words, 0, 0 != view->paths_on_device)) return st;
+		}
+		else
+		{
+			// variant_graph.cc:453: paths_by_chrom_copy_and_edge = transpose_matrix(paths_by_edge_and_chrom_copy)
+			if (int const st = dev_alloc(g.paths_he, path_words)) return st;
+			if (int const st = launch_transpose_bits(g.paths_eh, g.h_pad, g.e_pad, g.paths_he, nullptr)) return st;
+		}
+		if (!view->paths_by_edge_and_chrom_copy)
+			if (int const st = launch_transpose_bits(g.paths_he, g.e_pad, g.h_pad, g.paths_eh, nullptr)) return st;
+	}
+
+	if (int const st = dev_alloc(g.tmpl, g.A_alloc)) return st;
+	if (int const st = launch_build_template(g, nullptr)) return st;
+	V2M_CUDA_TRY(cudaDeviceSynchronize());
+	*out = holder.release();
+	return V2M_OK;
+}
+
+int v2m_cuda_graph_free(v2m_graph_t g)
+{
+	delete g;
+	return V2M_OK;
+}
+
+int v2m_cuda_graph_aligned_length(v2m_graph_t g, uint64_t *out)
+{
+	if (!g || !out) return fail(V2M_ERR_ARGUMENT, "NULL argument");
+	*out = g->g.A;
+	return V2M_OK;
+}
+
+int v2m_cuda_graph_download_paths_by_chrom_copy_and_edge(v2m_graph_t g, uint64_t *dst)
+{
+	if (!g || !dst) return fail(V2M_ERR_ARGUMENT, "NULL argument");
+	V2M_CUDA_TRY(cudaMemcpy(dst, g->g.paths_he, g->g.Wh * g->g.e_pad * 8, cudaMemcpyDeviceToHost));
+	return V2M_OK;
+}
+
+int v2m_cuda_graph_download_template(v2m_graph_t g, uint8_t *dst)
+{
+	if (!g || !dst) return fail(V2M_ERR_ARGUMENT, "NULL argument");
+	V2M_CUDA_TRY(cudaMemcpy(dst, g->g.tmpl, g->g.A, cudaMemcpyDeviceToHost));
+	return V2M_OK;
+}
+
+
+// ---- plans ------------------------------------------------------------------------------------------------
+int v2m_cuda_plan_haplotypes(v2m_graph_t g, const uint32_t *copy_idx, uint32_t n_rows, v2m_plan_t *out)
+{
+	if (!g || !out || (n_rows && !copy_idx)) return fail(V2M_ERR_ARGUMENT, "plan_haplotypes: NULL argument");
+	*out = nullptr;
+	for (u32 i(0); i < n_rows; ++i)
+		if (V2M_PLOIDY_MAX != copy_idx[i] && copy_idx[i] >= g->g.H)
+			return fail(V2M_ERR_ARGUMENT, "plan_haplotypes: chromosome copy index out of range");
+	auto holder(std::make_unique<v2m_plan_s>());
+	holder->owner = g;
+	holder->p.graph = &g->g;
+	holder->p.n_rows = n_rows;
+	if (int const st = dev_alloc(holder->p.taken, u64(n_rows) * g->g.We)) return st;
+	u32 *d_idx(nullptr);
+	if (int const st = dev_upload(d_idx, copy_idx, n_rows)) return st;
+	int const st(launch_resolve_rows(g->g, g->g.paths_he, d_idx, n_rows, holder->p.taken, nullptr));
+	cudaError_t const err(cudaDeviceSynchronize());
+	cudaFree(d_idx);
+	if (st) return st;
+	if (cudaSuccess != err) return fail(V2M_ERR_CUDA, std::string("resolve_rows: ") + cudaGetErrorString(err));
+	*out = holder.release();
+	return V2M_OK;
+}
+
+int v2m_cuda_plan_founders(v2m_graph_t g, const uint64_t *cut_positions, uint64_t n_segments,
+	const uint32_t *assigned, uint32_t n_founders, v2m_plan_t *out)
+{
+	if (!g || !out || !cut_positions || (n_founders && n_segments && !assigned)) return fail(V2M_ERR_ARGUMENT, "plan_founders: NULL argument");
+	*out = nullptr;
+	if (n_segments < 1) return fail(V2M_ERR_ARGUMENT, "plan_founders: need at least one segment");
+	if (0 != cut_positions[0]) return fail(V2M_ERR_ARGUMENT, "plan_founders: first cut position must be node 0 (founder_sequence_greedy_output.cc:102)");
+	std::vector<u64> cut_edges(n_segments + 1);
+	for (u64 s(0); s <= n_segments; ++s)
+	{
+		u64 const node(cut_positions[s]);
+		if (node >= g->g.N || (s && node <= cut_positions[s - 1])) return fail(V2M_ERR_ARGUMENT, "plan_founders: cut positions must be increasing node ids");
+		cut_edges[s] = g->csum[node];
+	}
+	// The last segment runs to the end of the edge list whatever the final cut node is.
+	cut_edges[n_segments] = g->g.E;
+	for (u64 i(0); i < n_segments * n_founders; ++i)
+		if (V2M_PLOIDY_MAX != assigned[i] && assigned[i] >= g->g.H)
+			return fail(V2M_ERR_ARGUMENT, "plan_founders: assigned chromosome copy out of range");
+
+	auto holder(std::make_unique<v2m_plan_s>());
+	holder->owner = g;
+	holder->p.graph = &g->g;
+	holder->p.n_rows = n_founders;
+	if (int const st = dev_alloc(holder->p.taken, u64(n_founders) * g->g.We)) return st;
+	u64 *d_cut_edges(nullptr), *d_lines(nullptr);
+	u32 *d_assigned(nullptr);
+	int st(V2M_OK);
+	do
+	{
+		if ((st = dev_upload(d_cut_edges, cut_edges.data(), cut_edges.size()))) break;
+		if ((st = dev_upload(d_assigned, assigned, n_segments * n_founders))) break;
+		if ((st = dev_alloc(d_lines, u64(n_founders) * g->g.We))) break;
+		if ((st = launch_compose_founders(g->g, d_cut_edges, n_segments, d_assigned, n_founders, d_lines, nullptr))) break;
+		if ((st = launch_resolve_rows(g->g, d_lines, nullptr, n_founders, holder->p.taken, nullptr))) break;
+		cudaError_t const err(cudaDeviceSynchronize());
+		if (cudaSuccess != err) st = fail(V2M_ERR_CUDA, std::string("plan_founders: ") + cudaGetErrorString(err));
+	} while (false);
+	cudaFree(d_cut_edges); cudaFree(d_assigned); cudaFree(d_lines);
+	if (st) return st;
+	*out = holder.release();
+	return V2M_OK;
+}
+
+int v2m_cuda_plan_free(v2m_plan_t p)
+{
+	delete p;
+	return V2M_OK;
+}
+
+int v2m_cuda_plan_row_count(v2m_plan_t p, uint32_t *out)
+{
+	if (!p || !out) return fail(V2M_ERR_ARGUMENT, "NULL argument");
+	*out = p->p.n_rows;
+	return V2M_OK;
+}
+
+int v2m_cuda_plan_download_taken(v2m_plan_t p, uint64_t *dst)
+{
+	if (!p || !dst) return fail(V2M_ERR_ARGUMENT, "NULL argument");
+	V2M_CUDA_TRY(cudaMemcpy(dst, p->p.taken, u64(p->p.n_rows) * p->p.graph->We * 8, cudaMemcpyDeviceToHost));
+	return V2M_OK;
+}
+
+
+// ---- rows -------------------------------------------------------------------------------------------------
+static int check_emit_args(v2m_plan_t p, uint32_t row_begin, uint32_t row_end, uint64_t col_begin, uint64_t col_end)
+{
+	if (!p) return fail(V2M_ERR_ARGUMENT, "emit_rows: NULL plan");
+	if (row_begin > row_end || row_end > p->p.n_rows) return fail(V2M_ERR_ARGUMENT, "emit_rows: row range out of bounds");
+	if (col_begin > col_end || col_end > p->p.graph->A) return fail(V2M_ERR_ARGUMENT, "emit_rows: column range out of bounds");
+	return V2M_OK;
+}
+
+int v2m_cuda_emit_rows_device(v2m_plan_t p, uint32_t row_begin, uint32_t row_end, uint64_t col_begin, uint64_t col_end,
+	void *d_out, uint64_t pitch, void *stream)
+{
+	if (int const st = check_emit_args(p, row_begin, row_end, col_begin, col_end)) return st;
+	if (row_begin == row_end || col_begin == col_end) return V2M_OK;
+	if (!d_out) return fail(V2M_ERR_ARGUMENT, "emit_rows_device: NULL output");
+	if (0 != col_begin % 16 || 0 != pitch % 16 || 0 != reinterpret_cast<std::uintptr_t>(d_out) % 16 || pitch < col_end - col_begin)
+		return fail(V2M_ERR_ARGUMENT, "emit_rows_device: output, pitch and col_begin must be 16-byte aligned and pitch >= columns");
+	return launch_emit_rows(*p->p.graph, p->p.taken, row_begin, row_end, col_begin, col_end, d_out, pitch, false, static_cast<cudaStream_t>(stream));
+}
+
+int v2m_cuda_emit_rows(v2m_plan_t p, uint32_t row_begin, uint32_t row_end, uint64_t col_begin, uint64_t col_end,
+	uint8_t *out, uint64_t pitch)
+{
+	if (int const st = check_emit_args(p, row_begin, row_end, col_begin, col_end)) return st;
+	if (row_begin == row_end || col_begin == col_end) return V2M_OK;
+	if (!out || pitch < col_end - col_begin) return fail(V2M_ERR_ARGUMENT, "emit_rows: NULL output or pitch < columns");
+
+	// Device tiles start at a 16-byte column boundary; the first (col_begin % 16) bytes of each tile row are skipped on the way out.
+	u64 const cb(col_begin & ~u64(15));
+	u64 const skip(col_begin - cb);
+	u64 const width(col_end - col_begin);
+	u64 const d_pitch((col_end - cb + 15) & ~u64(15));
+	u64 const budget(u64(256) << 20);	// bytes per staging buffer
+	u32 const chunk_rows(u32(std::max<u64>(1, std::min<u64>(row_end - row_begin, budget / d_pitch))));
+
+	u8 *d_buf[2] = {nullptr, nullptr};
+	cudaStream_t streams[2] = {nullptr, nullptr};
+	int st(V2M_OK);
+	do
+	{
+		for (int i(0); i < 2 && !st; ++i)
+		{
+			if ((st = dev_alloc(d_buf[i], u64(chunk_rows) * d_pitch))) break;
+			if (cudaSuccess != cudaStreamCreateWithFlags(&streams[i], cudaStreamNonBlocking)) st = fail(V2M_ERR_CUDA, "cudaStreamCreate failed");
+		}
+		if (st) break;
+		int k(0);
+		for (u32 r0(row_begin); r0 < row_end && !st; r0 += chunk_rows, k ^= 1)
+		{
+			u32 const r1(std::min<u64>(row_end, u64(r0) + chunk_rows));
+			// Work on a stream is ordered, so buffer k is free again once its previous copy has been issued on the same stream.
+			if ((st = launch_emit_rows(*p->p.graph, p->p.taken, r0, r1, cb, col_end, d_buf[k], d_pitch, false, streams[k]))) break;
+			if (cudaSuccess != cudaMemcpy2DAsync(out + u64(r0 - row_begin) * pitch, pitch, d_buf[k] + skip, d_pitch, width, r1 - r0, cudaMemcpyDeviceToHost, streams[k]))
+				st = fail(V2M_ERR_CUDA, "D2H copy of rows failed");
+		}
+		for (int i(0); i < 2; ++i)
+			if (streams[i] && cudaSuccess != cudaStreamSynchronize(streams[i]) && !st) st = fail(V2M_ERR_CUDA, std::string("emit_rows: ") + cudaGetErrorString(cudaGetLastError()));
+	} while (false);
+	for (int i(0); i < 2; ++i)
+	{
+		if (streams[i]) cudaStreamDestroy(streams[i]);
+		cudaFree(d_buf[i]);
+	}
+	return st;
+}
+
+int v2m_cuda_time_emit_rows(v2m_plan_t p, uint32_t row_begin, uint32_t row_end, void *d_out, uint64_t pitch, int iters, float *ms_mean)
+{
+	if (!p || !ms_mean || iters < 1) return fail(V2M_ERR_ARGUMENT, "time_emit_rows: bad argument");
+	cudaEvent_t e0, e1;
+	V2M_CUDA_TRY(cudaEventCreate(&e0));
+	V2M_CUDA_TRY(cudaEventCreate(&e1));
+	int st(V2M_OK);
+	cudaEventRecord(e0, nullptr);
+	for (int i(0); i < iters && !st; ++i)
+		st = v2m_cuda_emit_rows_device(p, row_begin, row_end, 0, p->p.graph->A, d_out, pitch, nullptr);
+	cudaEventRecord(e1, nullptr);
+	cudaError_t const err(cudaEventSynchronize(e1));
+	float ms(0);
+	cudaEventElapsedTime(&ms, e0, e1);
+	cudaEventDestroy(e0); cudaEventDestroy(e1);
+	if (st) return st;
+	if (cudaSuccess != err) return fail(V2M_ERR_CUDA, std::string("time_emit_rows: ") + cudaGetErrorString(err));
+	*ms_mean = ms / iters;
+	return V2M_OK;
+}
+
+} // extern "C"
+
+
+// ---- whole-stream driver ------------------------------------------------------------------------------------
+namespace {
+
+	int write_all(int fd, void const *buf, size_t n)
+	{
+		auto const *p(static_cast<char const *>(buf));
+		while (n)
+		{
+			ssize_t const w(::write(fd, p, n));
+			if (w < 0)
+			{
+				if (EINTR == errno) continue;
+				return fail(V2M_ERR_STATE, std::string("write(2) failed: ") + std::strerror(errno));
+			}
+			p += w; n -= size_t(w);
+		}
+		return V2M_OK;
+	}
+}
+
+extern "C" int v2m_cuda_write_a2m(v2m_plan_t p, const char *ids, int unaligned, int fd, v2m_row_callback row_done, void *ctx)
+{
+	if (!p || (!ids && p->p.n_rows)) return fail(V2M_ERR_ARGUMENT, "write_a2m: NULL argument");
+	device_graph const &g(*p->p.graph);
+	u32 const n_rows(p->p.n_rows);
+	if (0 == n_rows) return V2M_OK;
+
+	std::vector<u64> lengths(n_rows, g.A);
+	if (unaligned)
+		if (int const st = v2m_cuda_plan_row_lengths(p, 1, lengths.data())) return st;
+
+	// Row blocks of up to ~128 MiB go through two pinned buffers: while block k is being written to fd,
+	// block k + 1 is produced and copied. Rows keep a 16-byte pitch on the device; headers are interleaved here.
+	u64 const max_len(*std::max_element(lengths.begin(), lengths.end()));
+	u64 const pitch((std::max<u64>(max_len, 1) + 15) & ~u64(15));
+	u32 const block_rows(u32(std::max<u64>(1, std::min<u64>(n_rows, (u64(128) << 20) / pitch))));
+	u8 *h_buf[2] = {nullptr, nullptr};
+	u8 *d_buf[2] = {nullptr, nullptr};
+	cudaStream_t streams[2] = {nullptr, nullptr};
+	int st(V2M_OK);
+
+	auto produce([&](u32 r0, int k) -> int {
+		u32 const r1(std::min<u64>(n_rows, u64(r0) + block_rows));
+		if (unaligned)
+		{
+			std::vector<u64> offsets(r1 - r0);
+			for (u32 r(r0); r < r1; ++r) offsets[r - r0] = u64(r - r0) * pitch;
+			return v2m_cuda_emit_rows_unaligned(p, r0, r1, offsets.data(), h_buf[k]);	// synchronous
+		}
+		if (int const s = launch_emit_rows(g, p->p.taken, r0, r1, 0, g.A, d_buf[k], pitch, false, streams[k])) return s;
+		if (cudaSuccess != cudaMemcpyAsync(h_buf[k], d_buf[k], u64(r1 - r0) * pitch, cudaMemcpyDeviceToHost, streams[k]))
+			return fail(V2M_ERR_CUDA, "write_a2m: D2H copy failed");
+		return V2M_OK;
+	});
+
+	do
+	{
+		for (int i(0); i < 2 && !st; ++i)
+		{
+			if (cudaSuccess != cudaMallocHost(reinterpret_cast<void **>(&h_buf[i]), u64(block_rows) * pitch)) { st = fail(V2M_ERR_CUDA, "write_a2m: cudaMallocHost failed"); break; }
+			if ((st = dev_alloc(d_buf[i], u64(block_rows) * pitch))) break;
+			if (cudaSuccess != cudaStreamCreateWithFlags(&streams[i], cudaStreamNonBlocking)) st = fail(V2M_ERR_CUDA, "write_a2m: cudaStreamCreate failed");
+		}
+		if (st) break;
+
+		char const *id(ids);
+		if ((st = produce(0, 0))) break;
+		int k(0);
+		for (u32 r0(0); r0 < n_rows && !st; r0 += block_rows, k ^= 1)
+		{
+			u32 const r1(std::min<u64>(n_rows, u64(r0) + block_rows));
+			if (r1 < n_rows && (st = produce(r1, k ^ 1))) break;
+			if (cudaSuccess != cudaStreamSynchronize(streams[k])) { st = fail(V2M_ERR_CUDA, std::string("write_a2m: ") + cudaGetErrorString(cudaGetLastError())); break; }
+			for (u32 r(r0); r < r1 && !st; ++r)
+			{
+				// '>' id '\n' bytes '\n' (sequence_writer.cc:35-36; haplotype_output.cc:56-57, 75-76)
+				std::string header(">");
+				header += id; header += '\n';
+				id += std::strlen(id) + 1;
+				if ((st = write_all(fd, header.data(), header.size()))) break;
+				if ((st = write_all(fd, h_buf[k] + u64(r - r0) * pitch, lengths[r]))) break;
+				if ((st = write_all(fd, "\n", 1))) break;
+				if (row_done) row_done(r, ctx);
+			}
+		}
+	} while (false);
+
+	for (int i(0); i < 2; ++i)
+	{
+		if (streams[i]) { cudaStreamSynchronize(streams[i]); cudaStreamDestroy(streams[i]); }
+		cudaFree(d_buf[i]);
+		if (h_buf[i]) cudaFreeHost(h_buf[i]);
+	}
+	return st;
+}
+
+extern "C" int v2m_cuda_time_transpose_bits(const void *d_src, uint64_t rows, uint64_t cols, void *d_dst, int iters, float *ms_mean)
+{
+	if (!ms_mean || iters < 1) return fail(V2M_ERR_ARGUMENT, "time_transpose_bits: bad argument");
+	cudaEvent_t e0, e1;
+	V2M_CUDA_TRY(cudaEventCreate(&e0));
+	V2M_CUDA_TRY(cudaEventCreate(&e1));
+	int st(V2M_OK);
+	cudaEventRecord(e0, nullptr);
+	for (int i(0); i < iters && !st; ++i)
+		st = v2m_cuda_transpose_bits_device(d_src, rows, cols, d_dst, nullptr);
+	cudaEventRecord(e1, nullptr);
+	cudaError_t const err(cudaEventSynchronize(e1));
+	float ms(0);
+	cudaEventElapsedTime(&ms, e0, e1);
+	cudaEventDestroy(e0); cudaEventDestroy(e1);
+	if (st) return st;
+	if (cudaSuccess != err) return fail(V2M_ERR_CUDA, std::string("time_transpose_bits: ") + cudaGetErrorString(err));
+	*ms_mean = ms / iters;
+	return V2M_OK;
+}
+
+// ---- CUDA events for callers without CUDA headers (bench.py times the launching stream with these) ------------------
+extern "C" void *v2m_cuda_event_create(void)
+{
+	cudaEvent_t ev(nullptr);
+	if (cudaSuccess != cudaEventCreate(&ev)) { fail(V2M_ERR_CUDA, "cudaEventCreate failed"); return nullptr; }
+	return ev;
+}
+
+extern "C" void v2m_cuda_event_destroy(void *ev) { if (ev) cudaEventDestroy(static_cast<cudaEvent_t>(ev)); }
+
+extern "C" int v2m_cuda_event_record(void *ev, void *stream)
+{
+	V2M_CUDA_TRY(cudaEventRecord(static_cast<cudaEvent_t>(ev), static_cast<cudaStream_t>(stream)));
+	return V2M_OK;
+}
+
+extern "C" int v2m_cuda_event_elapsed_ms(void *e0, void *e1, float *ms)
+{
+	V2M_CUDA_TRY(cudaEventSynchronize(static_cast<cudaEvent_t>(e1)));
+	V2M_CUDA_TRY(cudaEventElapsedTime(ms, static_cast<cudaEvent_t>(e0), static_cast<cudaEvent_t>(e1)));
+	return V2M_OK;
+}

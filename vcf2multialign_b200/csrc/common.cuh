@@ -1,0 +1,69 @@
+// Shared helpers for the sm_100a kernels of libv2m_cuda.so.
+#pragma once
+
+#include <cstdint>
+#include <cstdio>
+#include <string>
+
+#include <cuda_runtime.h>
+
+namespace v2m {
+
+using u8 = std::uint8_t;
+using u32 = std::uint32_t;
+using u64 = std::uint64_t;
+
+constexpr u32 PLOIDY_MAX = 0xffffffffu;
+
+// Thread-local error text behind v2m_cuda_last_error().
+std::string &last_error();
+int fail(int status, std::string msg);
+void count_launch(unsigned n = 1);
+
+#define V2M_CUDA_TRY(expr) do { cudaError_t const err_((expr)); if (cudaSuccess != err_) \
+	return ::v2m::fail(2, std::string(#expr) + ": " + cudaGetErrorString(err_)); } while (0)
+
+#define V2M_CHECK_LAUNCH(name) do { cudaError_t const err_(cudaGetLastError()); if (cudaSuccess != err_) \
+	return ::v2m::fail(2, std::string("launch of " name ": ") + cudaGetErrorString(err_)); ::v2m::count_launch(); } while (0)
+
+// Per-edge record used by row emission: aligned span [a0, a1) and the label's place in the flattened label store.
+struct edge_rec { u32 a0, a1, label_off, label_len; };
+static_assert(16 == sizeof(edge_rec));
+
+// 128-bit streaming-friendly global accesses.
+__device__ __forceinline__ uint4 ld_nc_v4(void const *p)
+{
+	uint4 r;
+	asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+	return r;
+}
+
+__device__ __forceinline__ void st_v4(void *p, uint4 const &v)
+{
+	asm volatile("st.global.v4.u32 [%0], {%1, %2, %3, %4};" :: "l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+
+__device__ __forceinline__ void st_cs_v4(void *p, uint4 const &v)
+{
+	asm volatile("st.global.cs.v4.u32 [%0], {%1, %2, %3, %4};" :: "l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+
+// In-register 32×32 bit-matrix transpose, LSB-first on both sides: on return bit i of a[j] is what bit j of a[i] was.
+// Five block-swap stages (16, 8, 4, 2, 1); with full unrolling a[] lives in registers.
+__host__ __device__ __forceinline__ void transpose32(u32 (&a)[32])
+{
+	u32 m(0x0000ffffu);
+#pragma unroll
+	for (int j = 16; j != 0; j >>= 1, m ^= (m << j))
+	{
+#pragma unroll
+		for (int k = 0; k < 32; k = (k + j + 1) & ~j)
+		{
+			u32 const t(((a[k] >> j) ^ a[k + j]) & m);
+			a[k + j] ^= t;
+			a[k] ^= (t << j);
+		}
+	}
+}
+
+} // namespace v2m

@@ -1,0 +1,64 @@
+// Device-resident form of v2m::variant_graph (include/vcf2multialign/variant_graph.hh:57-66) + the reference.
+// HBM layout (all arrays 256-byte aligned by cudaMalloc):
+//   ref          L bytes                               reference sequence, verbatim
+//   refpos       N × u32                               reference_positions
+//   alnpos       N × u32                               aligned_positions (A = alnpos[N-1] < 2^32)
+//   edge_src     E_pad × u32                           source node of each ALT edge (from alt_edge_count_csum)
+//   edge_tgt     E_pad × u32                           alt_edge_targets
+//   edges        E_pad × 16 B  (edge_rec)              aligned span [aln[src], aln[tgt]) + label offset/length
+//   label_chars  Σ|label| bytes                        alt_edge_labels, flattened
+//   paths_eh     E_pad × (H_pad/64) × u64              paths_by_edge_and_chrom_copy.values(): one line per edge
+//   paths_he     H_pad × (E_pad/64) × u64              paths_by_chrom_copy_and_edge.values(): one line per chromosome copy
+//   tmpl         A_alloc bytes                         REF-aligned template (A rounded up to a whole K2 tile)
+//   tile_edges   ⌈A / K2_TCOL⌉ × uint2                 per column tile: (first edge whose span can reach into the tile,
+//                                                      first edge that starts at or after the tile's end)
+#pragma once
+
+#include <cuda_runtime.h>
+
+#include "common.cuh"
+
+namespace v2m {
+
+constexpr int K2_TCOL = 4096;			// columns per emit_rows tile
+constexpr int K2_THREADS = 256;
+constexpr int K2_ROWS_PER_CTA = 64;
+
+struct device_graph
+{
+	int			device{};
+	u64			N{}, E{}, L{}, A{}, A_alloc{};
+	u64			h_pad{}, e_pad{};
+	u64			Wh{}, We{};					// words per edge line / per chromosome-copy line
+	u32			H{};
+	u64			n_tiles{};
+	u64			label_bytes{};
+
+	u8			*ref{};
+	u32			*refpos{}, *alnpos{};
+	u32			*edge_src{}, *edge_tgt{};
+	edge_rec	*edges{};
+	u8			*label_chars{};
+	u64			*paths_eh{}, *paths_he{};
+	u8			*tmpl{};
+	uint2		*tile_edges{};
+	u64			*edge_of_node{};			// N + 1: alt_edge_count_csum (host copy kept for cut → edge index)
+};
+
+// A set of output rows resolved on the device: taken-edge bit lines, one per row.
+struct device_plan
+{
+	device_graph const	*graph{};
+	u32					n_rows{};
+	u64					*taken{};			// n_rows × We
+	bool				lengths_ready{};
+};
+
+int launch_transpose_bits(void const *d_src, u64 rows, u64 cols, void *d_dst, cudaStream_t stream);
+int launch_build_template(device_graph const &g, cudaStream_t stream);
+int launch_compose_founders(device_graph const &g, u64 const *d_cut_edges, u64 n_segments, u32 const *d_assigned, u32 n_founders, u64 *d_out, cudaStream_t stream);
+int launch_resolve_rows(device_graph const &g, u64 const *d_lines, u32 const *d_line_idx, u32 n_rows, u64 *d_taken, cudaStream_t stream);
+int launch_emit_rows(device_graph const &g, u64 const *d_taken, u32 row_begin, u32 row_end, u64 col_begin, u64 col_end,
+	void *d_out, u64 pitch, bool streaming, cudaStream_t stream);
+
+} // namespace v2m

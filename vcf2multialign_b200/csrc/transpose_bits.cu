@@ -1,0 +1,100 @@
+// K1 transpose_bits — the device side of v2m::transpose_matrix
+// (reference: libvcf2multialign/transpose_matrix.cc:41-109; called once per graph at variant_graph.cc:453).
+//
+// dst(x, y) = src(y, x) on libbio's column-major, LSB-first packed bit matrices. Seen as arrays of 32-bit words
+// (little-endian halves of the 64-bit words), the source is C "lines" (its columns) of R/32 words and the destination
+// R lines of C/32 words.
+//
+// One CTA moves a tile of TC = 512 source lines × 1024 bits (32 words):
+//   load    512 threads × 16 passes of 8-byte loads (lines are only 8-byte aligned in general: R/8 bytes per line,
+//           R % 64 == 0), into shared memory with the 8-byte pair index XOR-swizzled by the line group, so that the
+//           transposing reads below hit 32 distinct banks;
+//   compute every thread owns one 32×32 sub-tile: 32 conflict-free LDS, five block-swap stages in registers
+//           (common.cuh:transpose32) — ~12 instructions per 128 B per warp, an order of magnitude fewer than 32
+//           ballots per sub-tile, which would leave the kernel issue-bound instead of HBM-bound;
+//   store   lanes are laid out 16 line groups × 2 word columns, so each STG.32 of a warp writes two full 64-byte
+//           runs of two destination lines; consecutive CTAs (blockIdx.x) extend the same destination lines, so the
+//           126 MB L2 merges them into full lines before write-back.
+//
+// Algorithmic bytes: 2 · R · C / 8 (each bit read once, written once). Roofline: HBM read + write.
+#include "common.cuh"
+
+namespace v2m {
+
+constexpr int K1_TC = 512;			// source lines per tile
+constexpr int K1_TW = 32;			// 32-bit words per line per tile (1024 bits)
+constexpr int K1_THREADS = 512;
+
+__global__ void __launch_bounds__(K1_THREADS, 2)
+transpose_bits_kernel(u64 const * __restrict__ src, u32 * __restrict__ dst, u64 const R64, u64 const C)
+{
+	// R64 = source rows / 64 = 64-bit words per source line; C = number of source lines.
+	extern __shared__ __align__(16) u64 tile[];					// K1_TC * K1_TW / 2 words = 64 KiB (dynamic: above the 48 KiB static limit)
+
+	u64 const c0(u64(blockIdx.x) * K1_TC);
+	u64 const p0(u64(blockIdx.y) * (K1_TW / 2));				// first 64-bit word (pair) of the row band
+	unsigned const tid(threadIdx.x);
+
+	// ---- load -------------------------------------------------------------------------------------------
+	{
+		unsigned const q(tid & 15);								// pair within the 128-byte piece of a line
+		unsigned const l_in_pass(tid >> 4);						// 32 lines per pass
+		bool const pair_ok(p0 + q < R64);
+		u64 vals[K1_TC / 32];
+#pragma unroll
+		for (int p = 0; p < K1_TC / 32; ++p)
+		{
+			u64 const line(c0 + 32 * p + l_in_pass);
+			vals[p] = (pair_ok && line < C) ? __ldg(src + line * R64 + p0 + q) : 0;
+		}
+#pragma unroll
+		for (int p = 0; p < K1_TC / 32; ++p)
+		{
+			unsigned const l(32 * p + l_in_pass);
+			tile[l * 16 + (q ^ ((l >> 5) & 15))] = vals[p];		// line group = l >> 5 = p
+		}
+	}
+	__syncthreads();
+
+	// ---- transpose 32×32 sub-tiles in registers ------------------------------------------------------------
+	unsigned const lane(tid & 31), warp(tid >> 5);
+	unsigned const xl(lane & 15);								// line group (32 lines) within the tile
+	unsigned const yl(lane >> 4);								// low bit of the word column
+	unsigned const yw(2 * warp + yl);							// 32-bit word column within the tile, 0 … 31
+	u32 const *tile32(reinterpret_cast<u32 const *>(tile));
+	u32 a[32];
+	{
+		unsigned const phys(((warp ^ xl) << 1) | yl);			// swizzled word index inside the line
+#pragma unroll
+		for (int i = 0; i < 32; ++i)
+			a[i] = tile32[(32 * xl + i) * 32 + phys];
+	}
+	transpose32(a);
+
+	// ---- store ---------------------------------------------------------------------------------------------
+	u64 const C32(C / 32);
+	u64 const xw(c0 / 32 + xl);									// destination word within the line
+	u64 const r0(64 * p0 + 32 * yw);							// first destination line of this sub-tile
+	if (xw < C32 && r0 < 64 * R64)								// rows are a multiple of 64, sub-tiles of 32: all-or-nothing
+	{
+		u32 *out(dst + r0 * C32 + xw);
+#pragma unroll
+		for (int j = 0; j < 32; ++j)
+			out[u64(j) * C32] = a[j];
+	}
+}
+
+
+int launch_transpose_bits(void const *d_src, u64 rows, u64 cols, void *d_dst, cudaStream_t stream)
+{
+	if (0 == cols || 0 == rows) return 0;
+	u64 const R64(rows / 64);
+	dim3 const grid(unsigned((cols + K1_TC - 1) / K1_TC), unsigned((R64 + K1_TW / 2 - 1) / (K1_TW / 2)));
+	constexpr int smem_bytes(K1_TC * (K1_TW / 2) * sizeof(u64));
+	V2M_CUDA_TRY(cudaFuncSetAttribute(transpose_bits_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));	// per device
+	transpose_bits_kernel<<<grid, K1_THREADS, smem_bytes, stream>>>(static_cast<u64 const *>(d_src), static_cast<u32 *>(d_dst), R64, cols);
+	V2M_CHECK_LAUNCH("transpose_bits_kernel");
+	return 0;
+}
+
+} // namespace v2m
