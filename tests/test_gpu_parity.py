@@ -239,3 +239,53 @@ def test_haplotype_output_separate(v2m, tmp_path):
         assert sorted(os.listdir(d)) == sorted(n for n, _ in exp)
         for name, data in exp:
             assert (d / name).read_bytes() == data, name
+
+
+# ---- --unaligned -----------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("seed", range(12))
+def test_unaligned_rows_random_graphs(v2m, tmp_path, seed):
+    """sequence_writer.cc:80 with should_output_unaligned: no gap fill; row lengths and bytes against the oracle walk."""
+    og = rg.random_oracle_graph(str(tmp_path), 900 + seed, ref_len=400 + 977 * seed, n_records=30 + 60 * seed, n_samples=3 + seed % 4,
+                                ploidy=1 + seed % 2, long_del_prob=0.06 if seed % 2 else 0.0)
+    a = og.arrays()
+    dg, g = _device_graph(v2m, og)
+    H = a["total_copies"]
+    idx = list(range(H)) + [orc.PLOIDY_MAX]
+    plan = dg.plan_haplotypes(idx)
+    exp = [og.output_sequence(h, None, True) for h in idx]
+    assert [int(x) for x in plan.row_lengths(True)] == [len(e) for e in exp]
+    assert [int(x) for x in plan.row_lengths(False)] == [int(a["aligned_positions"][-1])] * len(idx)
+    got = plan.emit_rows_unaligned()
+    for i, h in enumerate(idx):
+        assert got[i] == exp[i], (seed, h)
+    if H >= 3:
+        part = plan.emit_rows_unaligned(1, 3)
+        assert part == exp[1:3]
+
+
+def test_unaligned_multi_tile(v2m, tmp_path):
+    og = rg.random_oracle_graph(str(tmp_path), 4321, ref_len=30000, n_records=2000, n_samples=5, ploidy=2, long_del_prob=0.03)
+    a = og.arrays()
+    dg, g = _device_graph(v2m, og)
+    H = a["total_copies"]
+    plan = dg.plan_haplotypes(list(range(H)))
+    got = plan.emit_rows_unaligned()
+    for h in range(H):
+        assert got[h] == og.output_sequence(h, None, True), h
+
+
+def test_haplotype_output_unaligned_stream_and_separate(v2m, tmp_path):
+    og = rg.random_oracle_graph(str(tmp_path), 555, ref_len=6000, n_records=500, n_samples=5, ploidy=2)
+    a = og.arrays()
+    g = v2m.VariantGraph.from_arrays(a)
+    dst = str(tmp_path / "u.fa")
+    v2m.haplotype_output("chrU", True, True).output_a2m(a["ref"], g, dst)
+    with open(dst, "rb") as f:
+        assert f.read() == og.haplotype_output_a2m("chrU", True, True)
+    d = tmp_path / "usep"
+    d.mkdir()
+    v2m.haplotype_output(None, False, True).output_separate(a["ref"], g, True, str(d))
+    exp = og.haplotype_output_separate(None, False, True, True)
+    assert sorted(os.listdir(d)) == sorted(n for n, _ in exp)
+    for name, data in exp:
+        assert (d / name).read_bytes() == data, name

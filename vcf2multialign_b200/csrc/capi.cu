@@ -60,7 +60,7 @@ namespace v2m {
 		{
 			cudaFree(g.ref); cudaFree(g.refpos); cudaFree(g.alnpos); cudaFree(g.edge_src); cudaFree(g.edge_tgt);
 			cudaFree(g.edges); cudaFree(g.label_chars); cudaFree(g.paths_eh); cudaFree(g.paths_he);
-			cudaFree(g.tmpl); cudaFree(g.tile_edges);
+			cudaFree(g.tmpl); cudaFree(g.tile_edges); cudaFree(g.edge_ref); cudaFree(g.ref_tile_edges);
 		}
 	};
 
@@ -68,9 +68,9 @@ namespace v2m {
 	{
 		device_plan				p;
 		graph_holder const		*owner{};
-		std::vector<u64>		unaligned_lengths;
+		std::vector<u64>		unaligned_lengths;	// host copy of p.lengths once computed
 
-		~plan_holder() { cudaFree(p.taken); }
+		~plan_holder() { cudaFree(p.taken); cudaFree(p.prefix); cudaFree(p.lengths); }
 	};
 }
 
@@ -212,6 +212,7 @@ int v2m_cuda_graph_upload(const v2m_graph_view *view, v2m_graph_t *out)
 			return fail(V2M_ERR_ARGUMENT, "graph_upload: node positions must be strictly increasing");
 	}
 	std::vector<edge_rec> edges(g.e_pad, edge_rec{0, 0, 0, 0});
+	std::vector<uint2> edge_ref(g.e_pad, make_uint2(0, 0));
 	for (u64 n(0); n < N; ++n)
 	{
 		u64 const lb(holder->csum[n]), rb(holder->csum[n + 1]);
@@ -226,30 +227,36 @@ int v2m_cuda_graph_upload(const v2m_graph_view *view, v2m_graph_t *out)
 			if (hi >= (u64(1) << 32)) return fail(V2M_ERR_ARGUMENT, "graph_upload: label store too large");
 			edge_src[e] = u32(n); edge_tgt[e] = u32(t);
 			edges[e] = edge_rec{alnpos[n], alnpos[t], u32(lo), u32(hi - lo)};
+			edge_ref[e] = make_uint2(refpos[n], refpos[t]);
 		}
 	}
 	g.label_bytes = E ? view->label_offsets[E] : 0;
 
-	// Per column tile: edges whose span may intersect it.
-	std::vector<uint2> tile_edges(std::max<u64>(g.n_tiles, 1), make_uint2(0, 0));
-	{
+	// Per tile of K2_TCOL positions (aligned columns / reference positions): the edges whose span may intersect it.
+	auto const tile_edge_ranges([E](u64 const n_tiles, auto const &span /* e → (begin, end) */) {
+		std::vector<uint2> out(std::max<u64>(n_tiles, 1), make_uint2(0, 0));
 		u64 e_lo(0), e_hi(0), e_back(0);
-		u32 reach(0);			// max a1 over edges [0, e_back]
-		for (u64 b(0); b < g.n_tiles; ++b)
+		u32 reach(0);			// max span end over edges [0, e_back]
+		for (u64 b(0); b < n_tiles; ++b)
 		{
 			u64 const t0(b * K2_TCOL), t1(t0 + K2_TCOL);
-			while (e_lo < E && edges[e_lo].a0 < t0) ++e_lo;
-			while (e_hi < E && edges[e_hi].a0 < t1) ++e_hi;
-			// first edge whose running maximum of a1 exceeds t0
+			while (e_lo < E && span(e_lo).x < t0) ++e_lo;
+			while (e_hi < E && span(e_hi).x < t1) ++e_hi;
+			// first edge whose running maximum of span ends exceeds t0
 			while (e_back < e_lo)
 			{
-				reach = std::max(reach, edges[e_back].a1);
+				reach = std::max(reach, span(e_back).y);
 				if (reach > t0) break;
 				++e_back;
 			}
-			tile_edges[b] = make_uint2(unsigned(std::min(e_back, e_lo)), unsigned(e_hi));
+			out[b] = make_uint2(unsigned(std::min(e_back, e_lo)), unsigned(e_hi));
 		}
-	}
+		return out;
+	});
+	std::vector<uint2> const tile_edges(tile_edge_ranges(g.n_tiles, [&edges](u64 e){ return make_uint2(edges[e].a0, edges[e].a1); }));
+	g.ref_end = refpos[N - 1];
+	g.n_ref_tiles = (u64(g.ref_end) + K2_TCOL - 1) / K2_TCOL;
+	std::vector<uint2> const ref_tile_edges(tile_edge_ranges(g.n_ref_tiles, [&edge_ref](u64 e){ return edge_ref[e]; }));
 
 	if (int const st = dev_upload(g.ref, reinterpret_cast<u8 const *>(view->ref_seq), g.L, g.L + 16)) return st;
 	if (int const st = dev_upload(g.refpos, refpos.data(), N)) return st;
@@ -259,6 +266,8 @@ int v2m_cuda_graph_upload(const v2m_graph_view *view, v2m_graph_t *out)
 	if (int const st = dev_upload(g.edges, edges.data(), g.e_pad)) return st;
 	if (int const st = dev_upload(g.label_chars, reinterpret_cast<u8 const *>(view->label_chars), g.label_bytes, g.label_bytes + 16)) return st;
 	if (int const st = dev_upload(g.tile_edges, tile_edges.data(), tile_edges.size())) return st;
+	if (int const st = dev_upload(g.edge_ref, edge_ref.data(), g.e_pad)) return st;
+	if (int const st = dev_upload(g.ref_tile_edges, ref_tile_edges.data(), ref_tile_edges.size())) return st;
 
 	u64 const path_words(g.Wh * g.e_pad);
 	if (path_words)
@@ -470,6 +479,77 @@ int v2m_cuda_emit_rows(v2m_plan_t p, uint32_t row_begin, uint32_t row_end, uint6
 		if (streams[i]) cudaStreamDestroy(streams[i]);
 		cudaFree(d_buf[i]);
 	}
+	return st;
+}
+
+// ---- --unaligned ------------------------------------------------------------------------------------------------
+static int ensure_unaligned_prefix(v2m_plan_t p)
+{
+	if (p->p.prefix) return V2M_OK;
+	device_graph const &g(*p->p.graph);
+	u32 const n_rows(p->p.n_rows);
+	int *d_prefix(nullptr);
+	u64 *d_lengths(nullptr);
+	if (int const st = dev_alloc(d_prefix, u64(n_rows) * (g.We + 1))) return st;
+	if (int const st = dev_alloc(d_lengths, n_rows)) { cudaFree(d_prefix); return st; }
+	int st(launch_unaligned_prefix(g, p->p.taken, n_rows, d_prefix, d_lengths, nullptr));
+	p->unaligned_lengths.assign(n_rows, 0);
+	if (!st && n_rows && cudaSuccess != cudaMemcpy(p->unaligned_lengths.data(), d_lengths, u64(n_rows) * 8, cudaMemcpyDeviceToHost))
+		st = fail(V2M_ERR_CUDA, std::string("unaligned_prefix: ") + cudaGetErrorString(cudaGetLastError()));
+	if (st) { cudaFree(d_prefix); cudaFree(d_lengths); return st; }
+	p->p.prefix = d_prefix;
+	p->p.lengths = d_lengths;
+	return V2M_OK;
+}
+
+int v2m_cuda_plan_row_lengths(v2m_plan_t p, int unaligned, uint64_t *out)
+{
+	if (!p || (!out && p->p.n_rows)) return fail(V2M_ERR_ARGUMENT, "plan_row_lengths: NULL argument");
+	if (!unaligned)
+	{
+		std::fill(out, out + p->p.n_rows, p->p.graph->A);
+		return V2M_OK;
+	}
+	if (int const st = ensure_unaligned_prefix(p)) return st;
+	std::copy(p->unaligned_lengths.begin(), p->unaligned_lengths.end(), out);
+	return V2M_OK;
+}
+
+int v2m_cuda_emit_rows_unaligned(v2m_plan_t p, uint32_t row_begin, uint32_t row_end, const uint64_t *offsets, uint8_t *out)
+{
+	if (!p) return fail(V2M_ERR_ARGUMENT, "emit_rows_unaligned: NULL plan");
+	if (row_begin > row_end || row_end > p->p.n_rows) return fail(V2M_ERR_ARGUMENT, "emit_rows_unaligned: row range out of bounds");
+	if (row_begin == row_end) return V2M_OK;
+	if (!offsets || !out) return fail(V2M_ERR_ARGUMENT, "emit_rows_unaligned: NULL argument");
+	if (int const st = ensure_unaligned_prefix(p)) return st;
+	u32 const n(row_end - row_begin);
+	u64 extent(0);
+	for (u32 i(0); i < n; ++i) extent = std::max(extent, offsets[i] + p->unaligned_lengths[row_begin + i]);
+	if (0 == extent) return V2M_OK;
+	u8 *d_out(nullptr);
+	u64 *d_offsets(nullptr);
+	int st(V2M_OK);
+	do
+	{
+		if ((st = dev_alloc(d_out, extent))) break;
+		if ((st = dev_upload(d_offsets, offsets, n))) break;
+		if ((st = launch_emit_unaligned(*p->p.graph, p->p.taken, p->p.prefix, row_begin, row_end, d_offsets, d_out, nullptr))) break;
+		// Only the rows' own bytes are copied back; contiguous rows go in one copy.
+		u32 i(0);
+		while (i < n && !st)
+		{
+			u64 const b(offsets[i]);
+			u64 e(b + p->unaligned_lengths[row_begin + i]);
+			u32 j(i + 1);
+			while (j < n && offsets[j] == e) { e += p->unaligned_lengths[row_begin + j]; ++j; }
+			if (e > b && cudaSuccess != cudaMemcpyAsync(out + b, d_out + b, e - b, cudaMemcpyDeviceToHost, nullptr))
+				st = fail(V2M_ERR_CUDA, "emit_rows_unaligned: D2H copy failed");
+			i = j;
+		}
+		cudaError_t const err(cudaDeviceSynchronize());
+		if (!st && cudaSuccess != err) st = fail(V2M_ERR_CUDA, std::string("emit_rows_unaligned: ") + cudaGetErrorString(err));
+	} while (false);
+	cudaFree(d_out); cudaFree(d_offsets);
 	return st;
 }
 

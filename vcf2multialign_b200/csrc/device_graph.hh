@@ -12,6 +12,8 @@
 //   tmpl         A_alloc bytes                         REF-aligned template (A rounded up to a whole K2 tile)
 //   tile_edges   ⌈A / K2_TCOL⌉ × uint2                 per column tile: (first edge whose span can reach into the tile,
 //                                                      first edge that starts at or after the tile's end)
+//   edge_ref     E_pad × uint2                         reference span [refpos[src], refpos[tgt]) of each ALT edge (--unaligned)
+//   ref_tile_edges ⌈ref_end / K2_TCOL⌉ × uint2         tile_edges in reference coordinates (--unaligned)
 #pragma once
 
 #include <cuda_runtime.h>
@@ -42,6 +44,10 @@ struct device_graph
 	u64			*paths_eh{}, *paths_he{};
 	u8			*tmpl{};
 	uint2		*tile_edges{};
+	uint2		*edge_ref{};
+	uint2		*ref_tile_edges{};
+	u64			n_ref_tiles{};
+	u32			ref_end{};					// reference_positions.back(): where every walk stops
 	u64			*edge_of_node{};			// N + 1: alt_edge_count_csum (host copy kept for cut → edge index)
 };
 
@@ -51,7 +57,8 @@ struct device_plan
 	device_graph const	*graph{};
 	u32					n_rows{};
 	u64					*taken{};			// n_rows × We
-	bool				lengths_ready{};
+	int					*prefix{};			// --unaligned: n_rows × (We + 1) exclusive prefix sums of (|label| − REF span) over taken edges
+	u64					*lengths{};			// --unaligned: n_rows row lengths
 };
 
 int launch_transpose_bits(void const *d_src, u64 rows, u64 cols, void *d_dst, cudaStream_t stream);
@@ -60,5 +67,8 @@ int launch_compose_founders(device_graph const &g, u64 const *d_cut_edges, u64 n
 int launch_resolve_rows(device_graph const &g, u64 const *d_lines, u32 const *d_line_idx, u32 n_rows, u64 *d_taken, cudaStream_t stream);
 int launch_emit_rows(device_graph const &g, u64 const *d_taken, u32 row_begin, u32 row_end, u64 col_begin, u64 col_end,
 	void *d_out, u64 pitch, bool streaming, cudaStream_t stream);
+int launch_unaligned_prefix(device_graph const &g, u64 const *d_taken, u32 n_rows, int *d_prefix, u64 *d_lengths, cudaStream_t stream);
+int launch_emit_unaligned(device_graph const &g, u64 const *d_taken, int const *d_prefix, u32 row_begin, u32 row_end,
+	u64 const *d_offsets, void *d_out, cudaStream_t stream);
 
 } // namespace v2m

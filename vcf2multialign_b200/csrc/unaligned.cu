@@ -3,7 +3,8 @@
 // ref[refpos[src], refpos[tgt]) replaced by label(e). Output offset of reference byte p in row h is p + D_h(p), where
 // D_h(p) = Σ over taken edges that end at or before p of (|label| − REF span).
 //
-//   unaligned_prefix_kernel  one warp per row: per 64-edge word the exclusive prefix of those deltas, and the row length.
+//   unaligned_prefix_kernel  one warp per row: per 64-edge word the exclusive prefix of those deltas (We + 1 entries, the
+//                            last being the row total), and the row length refpos.back() + total.
 //   emit_unaligned_kernel    reference-coordinate tiles of 4096 bytes × row blocks; a warp walks the row's taken edges
 //                            that touch the tile and copies reference runs / labels to their shifted offsets.
 // Secondary mode (not the headline metric): byte-granular copies, coalesced per warp.
@@ -20,7 +21,7 @@ unaligned_prefix_kernel(u64 const * __restrict__ taken, u32 const n_rows, u64 co
 	u32 const row((blockIdx.x * blockDim.x + threadIdx.x) >> 5);
 	if (row >= n_rows) return;
 	u64 const *in(taken + u64(row) * We);
-	int *out(prefix + u64(row) * We);
+	int *out(prefix + u64(row) * (We + 1));			// We + 1 entries per row; the last one is the row total
 	int carry(0);
 	for (u64 wbase(0); wbase < We; wbase += 32)
 	{
@@ -45,7 +46,11 @@ unaligned_prefix_kernel(u64 const * __restrict__ taken, u32 const n_rows, u64 co
 		if (w < We) out[w] = carry + incl - delta;
 		carry += __shfl_sync(0xffffffffu, incl, 31);
 	}
-	if (0 == lane) lengths[row] = u64(long long(ref_end) + carry);
+	if (0 == lane)
+	{
+		out[We] = carry;
+		lengths[row] = u64((long long) ref_end + carry);
+	}
 }
 
 
@@ -80,7 +85,7 @@ emit_unaligned_kernel(unaligned_params const p)
 	{
 		u8 *orow(p.out + p.offsets[r - p.row_begin]);
 		u64 const *trow(p.taken + u64(r) * p.We);
-		long long D(te.x < te.y || w_lo < p.We ? p.prefix[u64(r) * p.We + w_lo] : 0);
+		long long D(p.prefix[u64(r) * (p.We + 1) + w_lo]);	// w_lo <= We
 		u32 cur(t0);
 		if (te.x < te.y)
 		{
