@@ -60,7 +60,7 @@ namespace v2m {
 		{
 			cudaFree(g.ref); cudaFree(g.refpos); cudaFree(g.alnpos); cudaFree(g.edge_src); cudaFree(g.edge_tgt);
 			cudaFree(g.edges); cudaFree(g.label_chars); cudaFree(g.paths_eh); cudaFree(g.paths_he);
-			cudaFree(g.tmpl); cudaFree(g.tile_edges); cudaFree(g.edge_ref); cudaFree(g.ref_tile_edges);
+			cudaFree(g.tmpl); cudaFree(g.tile_edges); cudaFree(g.tile_labels); cudaFree(g.edge_ref); cudaFree(g.ref_tile_edges);
 		}
 	};
 
@@ -254,6 +254,10 @@ int v2m_cuda_graph_upload(const v2m_graph_view *view, v2m_graph_t *out)
 		return out;
 	});
 	std::vector<uint2> const tile_edges(tile_edge_ranges(g.n_tiles, [&edges](u64 e){ return make_uint2(edges[e].a0, edges[e].a1); }));
+	std::vector<uint2> tile_labels(tile_edges.size(), make_uint2(0, 0));
+	for (u64 b(0); b < g.n_tiles; ++b)
+		if (tile_edges[b].x < tile_edges[b].y)
+			tile_labels[b] = make_uint2(edges[tile_edges[b].x].label_off, edges[tile_edges[b].y - 1].label_off + edges[tile_edges[b].y - 1].label_len);
 	g.ref_end = refpos[N - 1];
 	g.n_ref_tiles = (u64(g.ref_end) + K2_TCOL - 1) / K2_TCOL;
 	std::vector<uint2> const ref_tile_edges(tile_edge_ranges(g.n_ref_tiles, [&edge_ref](u64 e){ return edge_ref[e]; }));
@@ -264,8 +268,9 @@ int v2m_cuda_graph_upload(const v2m_graph_view *view, v2m_graph_t *out)
 	if (int const st = dev_upload(g.edge_src, edge_src.data(), g.e_pad)) return st;
 	if (int const st = dev_upload(g.edge_tgt, edge_tgt.data(), g.e_pad)) return st;
 	if (int const st = dev_upload(g.edges, edges.data(), g.e_pad)) return st;
-	if (int const st = dev_upload(g.label_chars, reinterpret_cast<u8 const *>(view->label_chars), g.label_bytes, g.label_bytes + 16)) return st;
+	if (int const st = dev_upload(g.label_chars, reinterpret_cast<u8 const *>(view->label_chars), g.label_bytes, g.label_bytes + 32)) return st;
 	if (int const st = dev_upload(g.tile_edges, tile_edges.data(), tile_edges.size())) return st;
+	if (int const st = dev_upload(g.tile_labels, tile_labels.data(), tile_labels.size())) return st;
 	if (int const st = dev_upload(g.edge_ref, edge_ref.data(), g.e_pad)) return st;
 	if (int const st = dev_upload(g.ref_tile_edges, ref_tile_edges.data(), ref_tile_edges.size())) return st;
 
@@ -433,7 +438,7 @@ int v2m_cuda_emit_rows_device(v2m_plan_t p, uint32_t row_begin, uint32_t row_end
 	if (!d_out) return fail(V2M_ERR_ARGUMENT, "emit_rows_device: NULL output");
 	if (0 != col_begin % 16 || 0 != pitch % 16 || 0 != reinterpret_cast<std::uintptr_t>(d_out) % 16 || pitch < col_end - col_begin)
 		return fail(V2M_ERR_ARGUMENT, "emit_rows_device: output, pitch and col_begin must be 16-byte aligned and pitch >= columns");
-	return launch_emit_rows(*p->p.graph, p->p.taken, row_begin, row_end, col_begin, col_end, d_out, pitch, false, static_cast<cudaStream_t>(stream));
+	return launch_emit_rows(*p->p.graph, p->p.taken, row_begin, row_end, col_begin, col_end, d_out, pitch, static_cast<cudaStream_t>(stream));
 }
 
 int v2m_cuda_emit_rows(v2m_plan_t p, uint32_t row_begin, uint32_t row_end, uint64_t col_begin, uint64_t col_end,
@@ -467,7 +472,7 @@ int v2m_cuda_emit_rows(v2m_plan_t p, uint32_t row_begin, uint32_t row_end, uint6
 		{
 			u32 const r1(std::min<u64>(row_end, u64(r0) + chunk_rows));
 			// Work on a stream is ordered, so buffer k is free again once its previous copy has been issued on the same stream.
-			if ((st = launch_emit_rows(*p->p.graph, p->p.taken, r0, r1, cb, col_end, d_buf[k], d_pitch, false, streams[k]))) break;
+			if ((st = launch_emit_rows(*p->p.graph, p->p.taken, r0, r1, cb, col_end, d_buf[k], d_pitch, streams[k]))) break;
 			if (cudaSuccess != cudaMemcpy2DAsync(out + u64(r0 - row_begin) * pitch, pitch, d_buf[k] + skip, d_pitch, width, r1 - r0, cudaMemcpyDeviceToHost, streams[k]))
 				st = fail(V2M_ERR_CUDA, "D2H copy of rows failed");
 		}
@@ -626,7 +631,7 @@ extern "C" int v2m_cuda_write_a2m(v2m_plan_t p, const char *ids, int unaligned, 
 			for (u32 r(r0); r < r1; ++r) offsets[r - r0] = u64(r - r0) * pitch;
 			return v2m_cuda_emit_rows_unaligned(p, r0, r1, offsets.data(), h_buf[k]);	// synchronous
 		}
-		if (int const s = launch_emit_rows(g, p->p.taken, r0, r1, 0, g.A, d_buf[k], pitch, false, streams[k])) return s;
+		if (int const s = launch_emit_rows(g, p->p.taken, r0, r1, 0, g.A, d_buf[k], pitch, streams[k])) return s;
 		if (cudaSuccess != cudaMemcpyAsync(h_buf[k], d_buf[k], u64(r1 - r0) * pitch, cudaMemcpyDeviceToHost, streams[k]))
 			return fail(V2M_ERR_CUDA, "write_a2m: D2H copy failed");
 		return V2M_OK;

@@ -48,6 +48,58 @@ __device__ __forceinline__ void st_cs_v4(void *p, uint4 const &v)
 	asm volatile("st.global.cs.v4.u32 [%0], {%1, %2, %3, %4};" :: "l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
 }
 
+// ---- bulk async copies (TMA engine, SASS UBLKCP) and their mbarrier / proxy plumbing ----------------------------------
+__device__ __forceinline__ u32 smem_u32(void const *p) { return static_cast<u32>(__cvta_generic_to_shared(p)); }
+
+__device__ __forceinline__ void mbar_init(u64 *bar, u32 const count)
+{
+	asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(smem_u32(bar)), "r"(count) : "memory");
+}
+
+__device__ __forceinline__ void mbar_expect_tx(u64 *bar, u32 const bytes)
+{
+	asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+
+__device__ __forceinline__ void mbar_wait(u64 *bar, u32 const parity)
+{
+	asm volatile(
+		"{\n"
+		".reg .pred p;\n"
+		"WAIT_%=:\n"
+		"mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+		"@p bra DONE_%=;\n"
+		"bra WAIT_%=;\n"
+		"DONE_%=:\n"
+		"}" :: "r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+
+// Makes mbarrier.init visible to the async proxy before the first bulk copy that signals it.
+__device__ __forceinline__ void fence_mbar_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+
+// Orders this thread's generic-proxy shared-memory writes before subsequent async-proxy (bulk copy) reads.
+__device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+// global → shared, completion counted in bytes on `bar`. 16-byte aligned addresses, size % 16 == 0.
+__device__ __forceinline__ void bulk_g2s(void *smem_dst, void const *gsrc, u32 const bytes, u64 *bar)
+{
+	asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+		:: "r"(smem_u32(smem_dst)), "l"(gsrc), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+
+// shared → global as part of the calling thread's current bulk group. 16-byte aligned addresses, size % 16 == 0.
+__device__ __forceinline__ void bulk_s2g(void *gdst, void const *smem_src, u32 const bytes)
+{
+	asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;"
+		:: "l"(gdst), "r"(smem_u32(smem_src)), "r"(bytes) : "memory");
+}
+
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+
+// Waits until at most t_pending of the calling thread's bulk groups have not yet finished READING their shared-memory source.
+template <int t_pending>
+__device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read %0;" :: "n"(t_pending) : "memory"); }
+
 // In-register 32×32 bit-matrix transpose, LSB-first on both sides: on return bit i of a[j] is what bit j of a[i] was.
 // Five block-swap stages (16, 8, 4, 2, 1); with full unrolling a[] lives in registers.
 __host__ __device__ __forceinline__ void transpose32(u32 (&a)[32])

@@ -12,6 +12,7 @@
 //   tmpl         A_alloc bytes                         REF-aligned template (A rounded up to a whole K2 tile)
 //   tile_edges   ⌈A / K2_TCOL⌉ × uint2                 per column tile: (first edge whose span can reach into the tile,
 //                                                      first edge that starts at or after the tile's end)
+//   tile_labels  ⌈A / K2_TCOL⌉ × uint2                 per column tile: byte range of those edges' labels in label_chars
 //   edge_ref     E_pad × uint2                         reference span [refpos[src], refpos[tgt]) of each ALT edge (--unaligned)
 //   ref_tile_edges ⌈ref_end / K2_TCOL⌉ × uint2         tile_edges in reference coordinates (--unaligned)
 #pragma once
@@ -44,6 +45,7 @@ struct device_graph
 	u64			*paths_eh{}, *paths_he{};
 	u8			*tmpl{};
 	uint2		*tile_edges{};
+	uint2		*tile_labels{};				// per column tile: [begin, end) of its edges' bytes in label_chars
 	uint2		*edge_ref{};
 	uint2		*ref_tile_edges{};
 	u64			n_ref_tiles{};
@@ -66,7 +68,7 @@ int launch_build_template(device_graph const &g, cudaStream_t stream);
 int launch_compose_founders(device_graph const &g, u64 const *d_cut_edges, u64 n_segments, u32 const *d_assigned, u32 n_founders, u64 *d_out, cudaStream_t stream);
 int launch_resolve_rows(device_graph const &g, u64 const *d_lines, u32 const *d_line_idx, u32 n_rows, u64 *d_taken, cudaStream_t stream);
 int launch_emit_rows(device_graph const &g, u64 const *d_taken, u32 row_begin, u32 row_end, u64 col_begin, u64 col_end,
-	void *d_out, u64 pitch, bool streaming, cudaStream_t stream);
+	void *d_out, u64 pitch, cudaStream_t stream);
 int launch_unaligned_prefix(device_graph const &g, u64 const *d_taken, u32 n_rows, int *d_prefix, u64 *d_lengths, cudaStream_t stream);
 int launch_emit_unaligned(device_graph const &g, u64 const *d_taken, int const *d_prefix, u32 row_begin, u32 row_end,
 	u64 const *d_offsets, void *d_out, cudaStream_t stream);

@@ -15,8 +15,8 @@
 //   compose_founder_kernel  path bits of founder rows: per segment the bits of the assigned chromosome copy
 //                           (founder_sequence_writing_delegate::handle_node, founder_…cc:106-114).
 //   resolve_rows_kernel     K2a: path bits → taken bits, one warp per row, 2048 edges per step.
-//   emit_rows_kernel        K2b: rows × columns tile writer; template tile held in registers and streamed to every
-//                           row of the block with 128-bit stores, then the row's few taken edges are patched in.
+//   emit_rows_kernel        K2b: rows × columns tile writer; template tile + edge records staged in shared memory by
+//                           bulk async copies, rows assembled in shared memory and written by the TMA engine.
 //                           Algorithmic bytes: rows × columns written. Roofline: HBM write.
 #include "common.cuh"
 #include "device_graph.hh"
@@ -198,12 +198,40 @@ resolve_rows_kernel(u64 const * __restrict__ lines, u32 const * __restrict__ lin
 // ---------------------------------------------------------------------------------------------------------
 // K2b emit_rows
 // ---------------------------------------------------------------------------------------------------------
+// One CTA = one tile of K2_TCOL aligned columns × K2_ROWS_PER_CTA rows.
+//   stage   one thread issues three bulk async copies (TMA engine) global → shared: the tile of the REF template, the
+//           records of the ALT edges that can intersect the tile and those edges' label bytes (contiguous in the
+//           flattened label store), so that patching never leaves the SM;
+//   rows    each warp owns K2_ROWS_PER_CTA / 8 rows and two K2_TCOL-byte row buffers in shared memory. Per row: the
+//           template tile (kept in registers) is written to a buffer with 128-bit STS, the row's taken edges that
+//           touch the tile are patched in (label bytes + '-'), and one lane hands the finished buffer to the TMA
+//           engine (cp.async.bulk shared → global): the LSU issues no global stores at all, and HBM only ever sees
+//           whole 128-byte lines. The taken-edge words of all rows of a warp are fetched up front (independent loads
+//           in flight), so no row waits on a dependent global load chain.
+// Algorithmic bytes: rows × columns written (+ < 1 % reads). Roofline: HBM write.
+constexpr int K2_EDGE_CAP = 256;								// ALT edge records staged per tile (c2 averages ~100)
+constexpr int K2_LABEL_CAP = 2048;								// label bytes staged per tile (incl. ≤ 15 bytes of alignment slack)
+constexpr int K2_WARPS = K2_THREADS / 32;
+constexpr int K2_ROWS_PER_WARP = K2_ROWS_PER_CTA / K2_WARPS;
+constexpr int K2_CHUNKS = K2_TCOL / 512;						// 16-byte chunks of the tile per lane
+constexpr u32 K2_SHORT_PATCH = 16;								// longer spans are written by the whole warp
+
+struct emit_smem
+{
+	alignas(128) u8			tmpl[K2_TCOL];
+	alignas(128) edge_rec	edges[K2_EDGE_CAP];
+	alignas(128) u8			labels[K2_LABEL_CAP];
+	alignas(128) u8			rows[K2_WARPS][2][K2_TCOL];
+	alignas(8) u64			bar;
+};
+
 struct emit_params
 {
 	u8 const		*tmpl;
 	edge_rec const	*edges;
 	u8 const		*label_chars;
 	uint2 const		*tile_edges;	// per absolute tile of K2_TCOL columns: (first edge that can reach into it, first edge starting after it)
+	uint2 const		*tile_labels;	// per tile: byte range of those edges' labels in label_chars
 	u64 const		*taken;			// plan rows × We
 	u64				We;
 	u32				row_begin, row_end;
@@ -213,16 +241,61 @@ struct emit_params
 	u64				pitch;
 };
 
-__device__ __forceinline__ u8 patch_byte(edge_rec const &rec, u8 const * __restrict__ label_chars, u32 const col)
+// `labels` holds the label store from label offset `base` on (shared-memory window or, with base 0, the global array).
+__device__ __forceinline__ u8 patch_byte(edge_rec const &rec, u8 const *labels, u32 const base, u32 const col)
 {
 	u32 const k(col - rec.a0);
-	return k < rec.label_len ? label_chars[rec.label_off + k] : u8('-');
+	return k < rec.label_len ? labels[rec.label_off - base + k] : u8('-');
 }
 
-template <bool t_streaming>
-__global__ void __launch_bounds__(K2_THREADS)
+// Applies the taken edges of one 64-edge word (`wl`, the same value in all lanes; bit b ↔ edge e_base + b) to `buf`
+// (the row's tile in shared memory; buf[0] is column t0). Lane l looks at bits l and l + 32.
+__device__ __forceinline__ bool has_edges_bytes(uint2 const tl) { return tl.y > tl.x; }
+
+template <bool t_staged>
+__device__ __forceinline__ void patch_word(u64 const wl, u64 const e_base, u32 const e_first, edge_rec const *s_edges,
+	edge_rec const * __restrict__ g_edges, u8 const *labels, u32 const lab_base, u32 const t0, u32 const c0, u32 const c1, u8 *buf, unsigned const lane)
+{
+#pragma unroll
+	for (int half = 0; half < 2; ++half)
+	{
+		unsigned const b(lane + 32 * half);
+		edge_rec rec{};
+		u32 lo(0), hi(0);
+		if ((wl >> b) & 1)
+		{
+			u64 const e(e_base + b);
+			if constexpr (t_staged) rec = s_edges[e - e_first];
+			else rec = *reinterpret_cast<edge_rec const *>(&reinterpret_cast<uint4 const *>(g_edges)[e]);
+			lo = max(rec.a0, c0); hi = min(rec.a1, c1);
+			if (lo >= hi) { lo = 0; hi = 0; }
+		}
+		bool const is_long(hi - lo > K2_SHORT_PATCH);
+		if (!is_long)
+			for (u32 col(lo); col < hi; ++col) buf[col - t0] = patch_byte(rec, labels, lab_base, col);
+		// Long spans (large deletions / insertions): one at a time, by the whole warp.
+		unsigned m(__ballot_sync(0xffffffffu, is_long));
+		while (m)
+		{
+			int const l(__ffs(m) - 1);
+			m &= m - 1;
+			edge_rec r2;
+			r2.a0 = __shfl_sync(0xffffffffu, rec.a0, l);
+			r2.a1 = __shfl_sync(0xffffffffu, rec.a1, l);
+			r2.label_off = __shfl_sync(0xffffffffu, rec.label_off, l);
+			r2.label_len = __shfl_sync(0xffffffffu, rec.label_len, l);
+			u32 const lo2(__shfl_sync(0xffffffffu, lo, l)), hi2(__shfl_sync(0xffffffffu, hi, l));
+			for (u32 col(lo2 + lane); col < hi2; col += 32) buf[col - t0] = patch_byte(r2, labels, lab_base, col);
+		}
+	}
+}
+
+__global__ void __launch_bounds__(K2_THREADS, 3)
 emit_rows_kernel(emit_params const p)
 {
+	extern __shared__ __align__(128) u8 smem_raw[];
+	emit_smem &sm(*reinterpret_cast<emit_smem *>(smem_raw));
+
 	unsigned const lane(threadIdx.x & 31), warp(threadIdx.x >> 5);
 	u64 const tile(p.first_tile + blockIdx.x);
 	u64 const t0(tile * K2_TCOL);
@@ -230,95 +303,105 @@ emit_rows_kernel(emit_params const p)
 	u32 const rb0(p.row_begin + blockIdx.y * K2_ROWS_PER_CTA);
 	u32 const rb1(min(rb0 + K2_ROWS_PER_CTA, p.row_end));
 
-	// Template tile → registers (the same bytes go to every row of the block).
-	uint4 v[K2_TCOL / 512];
-#pragma unroll
-	for (int j = 0; j < K2_TCOL / 512; ++j)
-		v[j] = *reinterpret_cast<uint4 const *>(p.tmpl + t0 + j * 512 + lane * 16);
-
 	uint2 const te(p.tile_edges[tile]);
-	bool const has_edges(te.x < te.y);
-	u64 const w_lo(te.x / 64), w_hi(has_edges ? (te.y - 1) / 64 : 0);
+	u32 const n_e(te.y - te.x);
+	bool const has_edges(0 != n_e);
+	uint2 const tl(p.tile_labels[tile]);
+	u32 const lab_base(tl.x & ~15u);											// bulk copies start at 16-byte boundaries
+	u32 const lab_bytes(has_edges_bytes(tl) ? ((tl.y - lab_base + 15u) & ~15u) : 0);
+	bool const staged(n_e <= K2_EDGE_CAP && lab_bytes <= K2_LABEL_CAP);
+	u64 const w_lo(te.x / 64), w_hi(has_edges ? (te.y - 1) / 64 : w_lo);
+	u32 const n_words(has_edges ? u32(w_hi - w_lo + 1) : 0);
 
-	for (u32 r(rb0 + warp); r < rb1; r += K2_THREADS / 32)
+	// ---- stage the template tile and the tile's edge records ---------------------------------------------------------
+	if (0 == threadIdx.x)
 	{
-		u8 *orow(p.out + u64(r - p.row_begin) * p.pitch);	// column c lives at orow[c - col_begin]
-
-#pragma unroll
-		for (int j = 0; j < K2_TCOL / 512; ++j)
-		{
-			u64 const col(t0 + j * 512 + lane * 16);
-			if (col >= c0 && col + 16 <= c1)
-			{
-				if constexpr (t_streaming) st_cs_v4(orow + (col - p.col_begin), v[j]);
-				else st_v4(orow + (col - p.col_begin), v[j]);
-			}
-			else if (col + 16 > c0 && col < c1)
-			{
-				u32 const wds[4] = {v[j].x, v[j].y, v[j].z, v[j].w};
-#pragma unroll
-				for (int k = 0; k < 16; ++k)
-					if (col + k >= c0 && col + k < c1)
-						orow[col + k - p.col_begin] = u8(wds[k >> 2] >> (8 * (k & 3)));
-			}
-		}
-
-		if (!has_edges) continue;
-		__syncwarp();	// template bytes of all lanes are ordered before the patches below
-
-		u64 const *trow(p.taken + u64(r) * p.We);
-		for (u64 wbase(w_lo); wbase <= w_hi; wbase += 32)
-		{
-			u64 const w(wbase + lane);
-			u64 word(w <= w_hi ? trow[w] : 0);
-			if (w == w_lo) word &= ~u64(0) << (te.x % 64);
-			if (w == w_hi && 0 != te.y % 64) word &= (u64(1) << (te.y % 64)) - 1;
-
-			bool pending(false);
-			edge_rec prec{};
-			u32 plo(0), phi(0);
-			auto scan([&]{
-				while (word)
-				{
-					int const b(__ffsll((long long) word) - 1);
-					word &= word - 1;
-					edge_rec const rec(*reinterpret_cast<edge_rec const *>(&reinterpret_cast<uint4 const *>(p.edges)[64 * w + b]));
-					u32 const lo(max(u64(rec.a0), c0)), hi(min(u64(rec.a1), c1));
-					if (lo >= hi) continue;
-					if (hi - lo <= 32)
-					{
-						for (u32 col(lo); col < hi; ++col)
-							orow[col - p.col_begin] = patch_byte(rec, p.label_chars, col);
-					}
-					else
-					{
-						pending = true; prec = rec; plo = lo; phi = hi;
-						return;
-					}
-				}
-			});
-			scan();
-			// Long spans (large deletions / insertions) are written by the whole warp.
-			unsigned m;
-			while ((m = __ballot_sync(0xffffffffu, pending)))
-			{
-				int const l(__ffs(m) - 1);
-				edge_rec rec;
-				rec.a0 = __shfl_sync(0xffffffffu, prec.a0, l);
-				rec.a1 = __shfl_sync(0xffffffffu, prec.a1, l);
-				rec.label_off = __shfl_sync(0xffffffffu, prec.label_off, l);
-				rec.label_len = __shfl_sync(0xffffffffu, prec.label_len, l);
-				u32 const lo(__shfl_sync(0xffffffffu, plo, l)), hi(__shfl_sync(0xffffffffu, phi, l));
-				for (u32 col(lo + lane); col < hi; col += 32)
-					orow[col - p.col_begin] = patch_byte(rec, p.label_chars, col);
-				if (int(lane) == l)
-				{
-					pending = false;
-					scan();
-				}
-			}
-		}
+		mbar_init(&sm.bar, 1);
+		fence_mbar_init();
+		u32 const edge_bytes(staged ? n_e * u32(sizeof(edge_rec)) : 0);
+		u32 const label_bytes(staged ? lab_bytes : 0);
+		mbar_expect_tx(&sm.bar, K2_TCOL + edge_bytes + label_bytes);
+		bulk_g2s(sm.tmpl, p.tmpl + t0, K2_TCOL, &sm.bar);
+		if (edge_bytes) bulk_g2s(sm.edges, p.edges + te.x, edge_bytes, &sm.bar);
+		if (label_bytes) bulk_g2s(sm.labels, p.label_chars + lab_base, label_bytes, &sm.bar);
 	}
+
+	// Meanwhile: taken-edge words of this warp's rows (first 32 words of the tile's range; lane ↔ word).
+	auto const load_word([&](u32 const r, u32 const i) -> u64 {
+		if (i >= n_words) return 0;
+		u64 const w(w_lo + i);
+		u64 word(p.taken[u64(r) * p.We + w]);
+		if (w == w_lo) word &= ~u64(0) << (te.x % 64);
+		if (w == w_hi && 0 != te.y % 64) word &= (u64(1) << (te.y % 64)) - 1;
+		return word;
+	});
+	u64 tw[K2_ROWS_PER_WARP];
+#pragma unroll
+	for (int k = 0; k < K2_ROWS_PER_WARP; ++k)
+	{
+		u32 const r(rb0 + warp + k * K2_WARPS);
+		tw[k] = (r < rb1) ? load_word(r, lane) : 0;
+	}
+
+	__syncthreads();					// the barrier's initialisation is visible to every waiter
+	mbar_wait(&sm.bar, 0);
+
+	uint4 v[K2_CHUNKS];
+#pragma unroll
+	for (int j = 0; j < K2_CHUNKS; ++j)
+		v[j] = *reinterpret_cast<uint4 const *>(sm.tmpl + j * 512 + lane * 16);
+
+	// What one row hands to the TMA engine: the 16-byte aligned part of [c0, c1); a ragged end goes out byte-wise.
+	u32 const off0(u32(c0 - t0));
+	u32 const n_bytes(u32(c1 - c0));
+	u32 const bulk_bytes(n_bytes & ~15u);
+
+#pragma unroll
+	for (int k = 0; k < K2_ROWS_PER_WARP; ++k)
+	{
+		u32 const r(rb0 + warp + k * K2_WARPS);
+		if (r >= rb1) break;
+		u8 *buf(sm.rows[warp][k & 1]);
+		if (k >= 2)
+		{
+			if (0 == lane) bulk_wait_read<1>();		// the copy that last read this buffer (two rows ago) is done with it
+			__syncwarp();
+		}
+#pragma unroll
+		for (int j = 0; j < K2_CHUNKS; ++j)
+			*reinterpret_cast<uint4 *>(buf + j * 512 + lane * 16) = v[j];
+
+		if (has_edges)
+		{
+			__syncwarp();
+			for (u32 chunk(0); chunk < n_words; chunk += 32)
+			{
+				u64 const word(0 == chunk ? tw[k] : load_word(r, chunk + lane));
+				unsigned nonempty(__ballot_sync(0xffffffffu, 0 != word));
+				while (nonempty)
+				{
+					int const l(__ffs(nonempty) - 1);
+					nonempty &= nonempty - 1;
+					u64 const wl(__shfl_sync(0xffffffffu, word, l));
+					u64 const e_base(64 * (w_lo + chunk + l));
+					if (staged) patch_word<true>(wl, e_base, te.x, sm.edges, p.edges, sm.labels, lab_base, u32(t0), u32(c0), u32(c1), buf, lane);
+					else patch_word<false>(wl, e_base, te.x, sm.edges, p.edges, p.label_chars, 0, u32(t0), u32(c0), u32(c1), buf, lane);
+				}
+			}
+		}
+
+		fence_proxy_async_smem();
+		__syncwarp();
+		u8 *orow(p.out + u64(r - p.row_begin) * p.pitch + (c0 - p.col_begin));
+		if (0 == lane && bulk_bytes)
+		{
+			bulk_s2g(orow, buf + off0, bulk_bytes);
+			bulk_commit();
+		}
+		if (lane < n_bytes - bulk_bytes)
+			orow[bulk_bytes + lane] = buf[off0 + bulk_bytes + lane];
+	}
+	if (0 == lane) bulk_wait_read<0>();			// shared memory stays valid until the engine has read it
 }
 
 
@@ -354,11 +437,11 @@ int launch_resolve_rows(device_graph const &g, u64 const *d_lines, u32 const *d_
 }
 
 int launch_emit_rows(device_graph const &g, u64 const *d_taken, u32 row_begin, u32 row_end, u64 col_begin, u64 col_end,
-	void *d_out, u64 pitch, bool streaming, cudaStream_t stream)
+	void *d_out, u64 pitch, cudaStream_t stream)
 {
 	if (row_begin >= row_end || col_begin >= col_end) return 0;
 	emit_params p;
-	p.tmpl = g.tmpl; p.edges = g.edges; p.label_chars = g.label_chars; p.tile_edges = g.tile_edges;
+	p.tmpl = g.tmpl; p.edges = g.edges; p.label_chars = g.label_chars; p.tile_edges = g.tile_edges; p.tile_labels = g.tile_labels;
 	p.taken = d_taken; p.We = g.We;
 	p.row_begin = row_begin; p.row_end = row_end; p.col_begin = col_begin; p.col_end = col_end;
 	p.first_tile = col_begin / K2_TCOL;
@@ -369,8 +452,8 @@ int launch_emit_rows(device_graph const &g, u64 const *d_taken, u32 row_begin, u
 	u32 const row_blocks((n_rows + K2_ROWS_PER_CTA - 1) / K2_ROWS_PER_CTA);
 	if (row_blocks > 65535) return fail(1, "too many rows in one emit_rows launch");
 	dim3 const grid(unsigned(last_tile - p.first_tile + 1), row_blocks);
-	if (streaming) emit_rows_kernel<true><<<grid, K2_THREADS, 0, stream>>>(p);
-	else emit_rows_kernel<false><<<grid, K2_THREADS, 0, stream>>>(p);
+	V2M_CUDA_TRY(cudaFuncSetAttribute(emit_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sizeof(emit_smem))));	// per device
+	emit_rows_kernel<<<grid, K2_THREADS, sizeof(emit_smem), stream>>>(p);
 	V2M_CHECK_LAUNCH("emit_rows_kernel");
 	return 0;
 }
