@@ -212,7 +212,6 @@ resolve_rows_kernel(u64 const * __restrict__ lines, u32 const * __restrict__ lin
 constexpr int K2_EDGE_CAP = 256;								// ALT edge records staged per tile (c2 averages ~100)
 constexpr int K2_LABEL_CAP = 2048;								// label bytes staged per tile (incl. ≤ 15 bytes of alignment slack)
 constexpr int K2_WARPS = K2_THREADS / 32;
-constexpr int K2_ROWS_PER_WARP = K2_ROWS_PER_CTA / K2_WARPS;
 constexpr int K2_CHUNKS = K2_TCOL / 512;						// 16-byte chunks of the tile per lane
 constexpr u32 K2_SHORT_PATCH = 16;								// longer spans are written by the whole warp
 
@@ -241,53 +240,11 @@ struct emit_params
 	u64				pitch;
 };
 
-// `labels` holds the label store from label offset `base` on (shared-memory window or, with base 0, the global array).
-__device__ __forceinline__ u8 patch_byte(edge_rec const &rec, u8 const *labels, u32 const base, u32 const col)
+// `labels` is the label store seen from label offset 0: the global array, or the tile's staged window shifted back.
+__device__ __forceinline__ u8 patch_byte(edge_rec const &rec, u8 const *labels, u32 const col)
 {
 	u32 const k(col - rec.a0);
-	return k < rec.label_len ? labels[rec.label_off - base + k] : u8('-');
-}
-
-// Applies the taken edges of one 64-edge word (`wl`, the same value in all lanes; bit b ↔ edge e_base + b) to `buf`
-// (the row's tile in shared memory; buf[0] is column t0). Lane l looks at bits l and l + 32.
-__device__ __forceinline__ bool has_edges_bytes(uint2 const tl) { return tl.y > tl.x; }
-
-template <bool t_staged>
-__device__ __forceinline__ void patch_word(u64 const wl, u64 const e_base, u32 const e_first, edge_rec const *s_edges,
-	edge_rec const * __restrict__ g_edges, u8 const *labels, u32 const lab_base, u32 const t0, u32 const c0, u32 const c1, u8 *buf, unsigned const lane)
-{
-#pragma unroll
-	for (int half = 0; half < 2; ++half)
-	{
-		unsigned const b(lane + 32 * half);
-		edge_rec rec{};
-		u32 lo(0), hi(0);
-		if ((wl >> b) & 1)
-		{
-			u64 const e(e_base + b);
-			if constexpr (t_staged) rec = s_edges[e - e_first];
-			else rec = *reinterpret_cast<edge_rec const *>(&reinterpret_cast<uint4 const *>(g_edges)[e]);
-			lo = max(rec.a0, c0); hi = min(rec.a1, c1);
-			if (lo >= hi) { lo = 0; hi = 0; }
-		}
-		bool const is_long(hi - lo > K2_SHORT_PATCH);
-		if (!is_long)
-			for (u32 col(lo); col < hi; ++col) buf[col - t0] = patch_byte(rec, labels, lab_base, col);
-		// Long spans (large deletions / insertions): one at a time, by the whole warp.
-		unsigned m(__ballot_sync(0xffffffffu, is_long));
-		while (m)
-		{
-			int const l(__ffs(m) - 1);
-			m &= m - 1;
-			edge_rec r2;
-			r2.a0 = __shfl_sync(0xffffffffu, rec.a0, l);
-			r2.a1 = __shfl_sync(0xffffffffu, rec.a1, l);
-			r2.label_off = __shfl_sync(0xffffffffu, rec.label_off, l);
-			r2.label_len = __shfl_sync(0xffffffffu, rec.label_len, l);
-			u32 const lo2(__shfl_sync(0xffffffffu, lo, l)), hi2(__shfl_sync(0xffffffffu, hi, l));
-			for (u32 col(lo2 + lane); col < hi2; col += 32) buf[col - t0] = patch_byte(r2, labels, lab_base, col);
-		}
-	}
+	return k < rec.label_len ? labels[rec.label_off + k] : u8('-');
 }
 
 __global__ void __launch_bounds__(K2_THREADS, 3)
@@ -308,7 +265,7 @@ emit_rows_kernel(emit_params const p)
 	bool const has_edges(0 != n_e);
 	uint2 const tl(p.tile_labels[tile]);
 	u32 const lab_base(tl.x & ~15u);											// bulk copies start at 16-byte boundaries
-	u32 const lab_bytes(has_edges_bytes(tl) ? ((tl.y - lab_base + 15u) & ~15u) : 0);
+	u32 const lab_bytes(tl.y > tl.x ? ((tl.y - lab_base + 15u) & ~15u) : 0);
 	bool const staged(n_e <= K2_EDGE_CAP && lab_bytes <= K2_LABEL_CAP);
 	u64 const w_lo(te.x / 64), w_hi(has_edges ? (te.y - 1) / 64 : w_lo);
 	u32 const n_words(has_edges ? u32(w_hi - w_lo + 1) : 0);
@@ -326,22 +283,17 @@ emit_rows_kernel(emit_params const p)
 		if (label_bytes) bulk_g2s(sm.labels, p.label_chars + lab_base, label_bytes, &sm.bar);
 	}
 
-	// Meanwhile: taken-edge words of this warp's rows (first 32 words of the tile's range; lane ↔ word).
+	// Meanwhile: taken-edge words of this warp's first rows (lane ↔ word; the loop below stays two rows ahead).
 	auto const load_word([&](u32 const r, u32 const i) -> u64 {
-		if (i >= n_words) return 0;
+		if (r >= rb1 || i >= n_words) return 0;
 		u64 const w(w_lo + i);
 		u64 word(p.taken[u64(r) * p.We + w]);
 		if (w == w_lo) word &= ~u64(0) << (te.x % 64);
 		if (w == w_hi && 0 != te.y % 64) word &= (u64(1) << (te.y % 64)) - 1;
 		return word;
 	});
-	u64 tw[K2_ROWS_PER_WARP];
-#pragma unroll
-	for (int k = 0; k < K2_ROWS_PER_WARP; ++k)
-	{
-		u32 const r(rb0 + warp + k * K2_WARPS);
-		tw[k] = (r < rb1) ? load_word(r, lane) : 0;
-	}
+	u64 w_cur(load_word(rb0 + warp, lane));
+	u64 w_nxt(load_word(rb0 + warp + K2_WARPS, lane));
 
 	__syncthreads();					// the barrier's initialisation is visible to every waiter
 	mbar_wait(&sm.bar, 0);
@@ -355,12 +307,17 @@ emit_rows_kernel(emit_params const p)
 	u32 const off0(u32(c0 - t0));
 	u32 const n_bytes(u32(c1 - c0));
 	u32 const bulk_bytes(n_bytes & ~15u);
+	u32 const t0_32 = u32(t0), c0_32 = u32(c0), c1_32 = u32(c1);
 
-#pragma unroll
-	for (int k = 0; k < K2_ROWS_PER_WARP; ++k)
+	// Edge records and labels as seen from edge 0 / label offset 0 (generic pointers into shared memory when staged).
+	edge_rec const *erecs(staged ? sm.edges - te.x : p.edges);
+	u8 const *labels(staged ? sm.labels - lab_base : p.label_chars);
+
+	u32 k(0);
+#pragma unroll 1
+	for (u32 r(rb0 + warp); r < rb1; r += K2_WARPS, ++k)
 	{
-		u32 const r(rb0 + warp + k * K2_WARPS);
-		if (r >= rb1) break;
+		u64 const w_nn(load_word(r + 2 * K2_WARPS, lane));
 		u8 *buf(sm.rows[warp][k & 1]);
 		if (k >= 2)
 		{
@@ -374,18 +331,41 @@ emit_rows_kernel(emit_params const p)
 		if (has_edges)
 		{
 			__syncwarp();
+#pragma unroll 1
 			for (u32 chunk(0); chunk < n_words; chunk += 32)
 			{
-				u64 const word(0 == chunk ? tw[k] : load_word(r, chunk + lane));
-				unsigned nonempty(__ballot_sync(0xffffffffu, 0 != word));
-				while (nonempty)
+				u64 word(0 == chunk ? w_cur : load_word(r, chunk + lane));
+				u64 const e_base(64 * (w_lo + chunk + lane));
+				bool pending(false);
+				edge_rec prec{};
+				u32 plo(0), phi(0);
+#pragma unroll 1
+				for (;;)
 				{
-					int const l(__ffs(nonempty) - 1);
-					nonempty &= nonempty - 1;
-					u64 const wl(__shfl_sync(0xffffffffu, word, l));
-					u64 const e_base(64 * (w_lo + chunk + l));
-					if (staged) patch_word<true>(wl, e_base, te.x, sm.edges, p.edges, sm.labels, lab_base, u32(t0), u32(c0), u32(c1), buf, lane);
-					else patch_word<false>(wl, e_base, te.x, sm.edges, p.edges, p.label_chars, 0, u32(t0), u32(c0), u32(c1), buf, lane);
+					// Each lane applies the short patches of its word until it meets a long span (or runs out).
+					while (!pending && word)
+					{
+						int const b(__ffsll((long long) word) - 1);
+						word &= word - 1;
+						edge_rec const rec(*reinterpret_cast<edge_rec const *>(&reinterpret_cast<uint4 const *>(erecs)[e_base + b]));
+						u32 const lo(max(rec.a0, c0_32)), hi(min(rec.a1, c1_32));
+						if (lo >= hi) continue;
+						if (hi - lo <= K2_SHORT_PATCH)
+							for (u32 col(lo); col < hi; ++col) buf[col - t0_32] = patch_byte(rec, labels, col);
+						else { pending = true; prec = rec; plo = lo; phi = hi; }
+					}
+					// Long spans (large deletions / insertions) are written by the whole warp, one at a time.
+					unsigned const m(__ballot_sync(0xffffffffu, pending));
+					if (0 == m) break;
+					int const l(__ffs(m) - 1);
+					edge_rec rec;
+					rec.a0 = __shfl_sync(0xffffffffu, prec.a0, l);
+					rec.a1 = __shfl_sync(0xffffffffu, prec.a1, l);
+					rec.label_off = __shfl_sync(0xffffffffu, prec.label_off, l);
+					rec.label_len = __shfl_sync(0xffffffffu, prec.label_len, l);
+					u32 const lo(__shfl_sync(0xffffffffu, plo, l)), hi(__shfl_sync(0xffffffffu, phi, l));
+					for (u32 col(lo + lane); col < hi; col += 32) buf[col - t0_32] = patch_byte(rec, labels, col);
+					if (int(lane) == l) pending = false;
 				}
 			}
 		}
@@ -400,6 +380,7 @@ emit_rows_kernel(emit_params const p)
 		}
 		if (lane < n_bytes - bulk_bytes)
 			orow[bulk_bytes + lane] = buf[off0 + bulk_bytes + lane];
+		w_cur = w_nxt; w_nxt = w_nn;
 	}
 	if (0 == lane) bulk_wait_read<0>();			// shared memory stays valid until the engine has read it
 }
