@@ -143,17 +143,29 @@ int v2m_cuda_write_a2m(v2m_plan_t p, const char *ids, int unaligned, int fd, v2m
 
 /* --- K3: per-cut haplotype classes for founder_sequence_greedy_output::find_matchings
  *         (libvcf2multialign/founder_sequence_greedy_output.cc:213-253, 460-469; pbwt.hh:77-134) ----------- */
-/* For each cut c in 1 … n_cuts-1 (cut_positions[0] == 0), with segment edges [s, e) between cut c-1 and cut c:
- *   rhs_eq[(c-1)*H + h]   representative of h's class on [s, e) (the member first in the pBWT order at s)
+/* cut_positions: n_cuts node ids as in founder_sequence_greedy_output::cut_positions() (first 0, last the sink). Every
+ * segment must contain at least one ALT edge (true for cuts from find_initial_cut_positions_lambda_min,
+ * find_cut_positions.cc:129), otherwise V2M_ERR_ARGUMENT. For each cut c in 1 … n_cuts-1, with segment edges [s, e) between
+ * cut c-1 and cut c:
+ *   rhs_eq[(c-1)*H + h]   representative of h's class on [s, e) (the member first in the pBWT order at s); may be NULL
  *   distinct[c-1]         number of classes                    (rhs_distinct_eq_classes)
  *   first_class[c-1]      permutation.front() at the cut       (rhs_first_path_eq_class)
  *   first_is_ref[c-1]     rhs_first_path_is_ref accumulated over [s, e)
- *   joined triples (lhs_rep, rhs_rep, size) in permutation order for c ≥ 2: joined_offsets[c-1] … joined_offsets[c]
- *   index into joined (capacity joined_cap triples; V2M_ERR_ARGUMENT if too small, needed count in joined_offsets[n_cuts-1]).
- */
+ *   joined triples (lhs_rep, rhs_rep, size) in permutation order: joined_offsets[c-1] … joined_offsets[c] index into joined
+ *   (for c = 1 the lhs is V2M_PLOIDY_MAX: the single-segment case of :474-509). joined holds joined_cap triples; if that is
+ *   too small the call returns V2M_ERR_ARGUMENT with the needed count in joined_offsets[n_cuts-1].
+ * At most 8192 chromosome copies (the sweep keeps the pBWT state in shared memory). */
 int v2m_cuda_segment_classes(v2m_graph_t g, const uint64_t *cut_positions, uint64_t n_cuts,
                              uint32_t *rhs_eq, uint32_t *distinct, uint32_t *first_class, uint8_t *first_is_ref,
                              uint64_t *joined_offsets /* [n_cuts] */, uint32_t *joined, uint64_t joined_cap);
+
+/* founder_sequence_greedy_output::find_matchings(graph, founder_count) (founder_sequence_greedy_output.cc:154-512; declared
+ * include/vcf2multialign/output.hh:126): K3 on the device, then the greedy assignment on the host (same std::sort /
+ * std::multimap as the reference). assigned = m_assigned_samples: column-major lb::matrix, (n_cuts - 1) segments × founder_count,
+ * unassigned entries V2M_PLOIDY_MAX. *found = what the reference returns (0: fewer than two cut positions or no chromosome
+ * copies). Inputs on which the reference asserts (:355) or does not terminate (:309-319, :429-438) give V2M_ERR_STATE. */
+int v2m_cuda_find_matchings(v2m_graph_t g, const uint64_t *cut_positions, uint64_t n_cuts, uint32_t founder_count,
+                            int keep_ref_edges, uint32_t *assigned, int *found);
 
 /* --- synthetic workloads (measurement infrastructure) ------------------------------------------------ */
 /* Fills d_dst (device, e_pad × h_pad/64 words = paths_by_edge_and_chrom_copy) with LD-structured path bits that are a

@@ -289,3 +289,141 @@ def test_haplotype_output_unaligned_stream_and_separate(v2m, tmp_path):
     assert sorted(os.listdir(d)) == sorted(n for n, _ in exp)
     for name, data in exp:
         assert (d / name).read_bytes() == data, name
+
+
+# ---- K3: per-cut classes and find_matchings ---------------------------------------------------------------------------
+def _check_classes(v2m, og, dg, founders=2, label=""):
+    """K3 against the class data the oracle's pBWT sweep records at every cut; returns the oracle FounderOutput (or None)."""
+    f = orc.FounderOutput(og)
+    if not f.find_cut_positions(0):
+        return None
+    cuts = f.cut_positions()
+    oracle_failed = False
+    try:
+        f.find_matchings(founders)
+    except orc.OracleError:
+        oracle_failed = True            # the class data of every cut reached before the failure is still recorded
+    rec = f.recorded_classes()
+    got = dg.segment_classes(cuts)
+    assert len(got) == len(cuts) - 1
+    H = og.dims()[4]
+    for i, r in enumerate(rec):
+        g = got[i]
+        assert g["distinct"] == r["distinct"], (label, i)
+        assert g["first_class"] == r["first_class"], (label, i)
+        assert g["first_is_ref"] == r["first_is_ref"], (label, i)
+        assert np.array_equal(g["rhs_eq"], r["rhs_eq"]), (label, i)
+        if i >= 1:
+            assert np.array_equal(g["joined"], r["joined"]), (label, i, g["joined"], r["joined"])
+        else:
+            # single-segment form (founder_…cc:474-509): one run per class, lhs = PLOIDY_MAX
+            assert g["joined"].shape[0] == r["distinct"] and int(g["joined"][:, 2].sum()) == H
+            assert (g["joined"][:, 0] == v2m.PLOIDY_MAX).all()
+            assert sorted(g["joined"][:, 1].tolist()) == sorted(set(r["rhs_eq"].tolist()))
+    return None if oracle_failed else f
+
+
+def test_segment_classes_on_reference_goldens(v2m, expected, golden_dir):
+    for case in expected["founder_sequences"]:
+        d = os.path.join(golden_dir, "founder-sequences")
+        og = orc.Graph.from_files(os.path.join(d, case["fa"]), os.path.join(d, case["vcf"]), "1")
+        dg, g = _device_graph(v2m, og)
+        f = _check_classes(v2m, og, dg, 2, case["vcf"])
+        assert f is not None and f.cut_positions().tolist() == case["cuts"]
+
+
+def test_find_matchings_on_reference_goldens(v2m, expected, golden_dir):
+    """cut positions → assigned_samples → A2M text of tests/founder_sequences.cc:118-188, through the reference-shaped mirror."""
+    for case in expected["founder_sequences"]:
+        d = os.path.join(golden_dir, "founder-sequences")
+        og = orc.Graph.from_files(os.path.join(d, case["fa"]), os.path.join(d, case["vcf"]), "1")
+        dg, g = _device_graph(v2m, og)
+        out = v2m.founder_sequence_greedy_output(None, True, False, False)
+        out.set_cut_positions(case["cuts"])
+        assert out.find_matchings(dg, 2)
+        exp = np.array(case["assigned_colmajor"], np.uint32).reshape(-1, case["rows"]).T
+        assert np.array_equal(out.assigned_samples(), exp), (case["vcf"], out.assigned_samples(), exp)
+        import tempfile
+        with tempfile.TemporaryDirectory() as td:
+            dst = os.path.join(td, "out.a2m")
+            out.output_a2m(None, dg, dst)
+            assert open(dst).read() == case["a2m"], case["vcf"]
+
+
+@pytest.mark.parametrize("chunks", ["1", "2", "3", "5", None])
+def test_segment_classes_random_graphs(v2m, tmp_path, chunks, monkeypatch):
+    if chunks is None:
+        monkeypatch.delenv("V2M_K3_CHUNKS", raising=False)
+    else:
+        monkeypatch.setenv("V2M_K3_CHUNKS", chunks)
+    done = 0
+    for seed in range(12):
+        og = rg.random_oracle_graph(str(tmp_path), 900 + seed, ref_len=900, n_records=90 + 10 * seed, n_samples=4 + 3 * seed, ploidy=2,
+                                    overlap=bool(seed % 2), sv=bool(seed % 3), alt_freq=0.15 + 0.03 * seed)
+        dg, g = _device_graph(v2m, og)
+        _check_classes(v2m, og, dg, 3, f"seed {seed} chunks {chunks}")
+        done += 1
+    assert done == 12
+
+
+@pytest.mark.parametrize("n_samples,chunks", [(520, "4"), (1100, "6"), (2504, None)])
+def test_segment_classes_many_copies(v2m, n_samples, chunks, monkeypatch):
+    """More chromosome copies than one warp-word per warp (KW 2, 3 and the 5,008-copy shape of c3), LD-structured bits."""
+    from vcf2multialign_b200 import synth
+    if chunks is None:
+        monkeypatch.delenv("V2M_K3_CHUNKS", raising=False)
+    else:
+        monkeypatch.setenv("V2M_K3_CHUNKS", chunks)
+    w = synth.make_workload("custom", seed=5, ref_len=120_000, n_sites=2_400, n_samples=n_samples, with_paths=True)
+    g = w.graph
+    og = orc.Graph.from_arrays(dict(
+        reference_positions=g.reference_positions, aligned_positions=g.aligned_positions, alt_edge_targets=g.alt_edge_targets,
+        alt_edge_count_csum=g.alt_edge_count_csum, label_offsets=g.label_offsets, label_chars=g.label_chars,
+        paths_ec=g.paths_by_edge_and_chrom_copy, paths_ce=None, h_pad=g.h_pad, e_pad=g.e_pad, ploidy_csum=g.ploidy_csum,
+        sample_names=g.sample_names, ref=w.ref))
+    dg = v2m.DeviceGraph(g, w.ref)
+    f = _check_classes(v2m, og, dg, 25, f"synth {n_samples}")
+    assert f is not None
+    m = dg.find_matchings(f.cut_positions(), 25)
+    assert np.array_equal(m, f.assigned_samples())
+
+
+def test_find_matchings_random_graphs(v2m, tmp_path):
+    ok = failed = 0
+    for seed in range(40):
+        og = rg.random_oracle_graph(str(tmp_path), 1300 + seed, ref_len=700, n_records=70, n_samples=3 + seed % 9, ploidy=2,
+                                    overlap=bool(seed % 2), sv=False, alt_freq=0.25)
+        f = orc.FounderOutput(og, None, True, bool(seed % 4 == 0), False)
+        if not f.find_cut_positions(seed % 3 * 10):
+            continue
+        founders = 1 + seed % 5
+        dg, g = _device_graph(v2m, og)
+        try:
+            assert f.find_matchings(founders)
+        except orc.OracleError:
+            # inputs on which the reference itself asserts or does not terminate: the library reports them
+            with pytest.raises(v2m.V2MError):
+                dg.find_matchings(f.cut_positions(), founders, bool(seed % 4 == 0))
+            failed += 1
+            continue
+        m = dg.find_matchings(f.cut_positions(), founders, bool(seed % 4 == 0))
+        assert np.array_equal(m, f.assigned_samples()), (seed, m, f.assigned_samples())
+        ok += 1
+    assert ok >= 20
+
+
+def test_find_matchings_degenerate(v2m, golden_dir):
+    d = os.path.join(golden_dir, "founder-sequences")
+    og = orc.Graph.from_files(os.path.join(d, "test-1.fa"), os.path.join(d, "test-1.vcf"), "1")
+    dg, g = _device_graph(v2m, og)
+    assert dg.find_matchings([0], 2) is None                    # fewer than two cut positions (founder_…cc:162-163)
+    N = g.node_count()
+    # a single segment: the trivial case (founder_…cc:474-509)
+    f = orc.FounderOutput(og)
+    f.set_cut_positions([0, N - 1])
+    assert f.find_matchings(3)
+    assert np.array_equal(dg.find_matchings([0, N - 1], 3), f.assigned_samples())
+    with pytest.raises(v2m.V2MError):
+        dg.segment_classes([0, 2, 2, N - 1])                    # cut positions must increase
+    with pytest.raises(v2m.V2MError):
+        dg.segment_classes([1, N - 1])                          # first cut must be node 0

@@ -51,19 +51,6 @@ namespace v2m {
 		return 0;
 	}
 
-	struct graph_holder
-	{
-		device_graph		g;
-		std::vector<u64>	csum;	// host copy of alt_edge_count_csum: node id → first edge index
-
-		~graph_holder()
-		{
-			cudaFree(g.ref); cudaFree(g.refpos); cudaFree(g.alnpos); cudaFree(g.edge_src); cudaFree(g.edge_tgt);
-			cudaFree(g.edges); cudaFree(g.label_chars); cudaFree(g.paths_eh); cudaFree(g.paths_he);
-			cudaFree(g.tmpl); cudaFree(g.tile_edges); cudaFree(g.tile_labels); cudaFree(g.edge_ref); cudaFree(g.ref_tile_edges);
-		}
-	};
-
 	struct plan_holder
 	{
 		device_plan				p;
@@ -76,7 +63,6 @@ namespace v2m {
 
 using namespace v2m;
 
-struct v2m_graph_s : v2m::graph_holder {};
 struct v2m_plan_s : v2m::plan_holder {};
 
 

@@ -17,6 +17,8 @@
 //   ref_tile_edges ⌈ref_end / K2_TCOL⌉ × uint2         tile_edges in reference coordinates (--unaligned)
 #pragma once
 
+#include <vector>
+
 #include <cuda_runtime.h>
 
 #include "common.cuh"
@@ -73,4 +75,21 @@ int launch_unaligned_prefix(device_graph const &g, u64 const *d_taken, u32 n_row
 int launch_emit_unaligned(device_graph const &g, u64 const *d_taken, int const *d_prefix, u32 row_begin, u32 row_end,
 	u64 const *d_offsets, void *d_out, cudaStream_t stream);
 
+
+// What a v2m_graph_t points to: the device arrays plus the host copy of alt_edge_count_csum (node id → first edge index).
+struct graph_holder
+{
+	device_graph		g;
+	std::vector<u64>	csum;
+
+	~graph_holder()
+	{
+		cudaFree(g.ref); cudaFree(g.refpos); cudaFree(g.alnpos); cudaFree(g.edge_src); cudaFree(g.edge_tgt);
+		cudaFree(g.edges); cudaFree(g.label_chars); cudaFree(g.paths_eh); cudaFree(g.paths_he);
+		cudaFree(g.tmpl); cudaFree(g.tile_edges); cudaFree(g.tile_labels); cudaFree(g.edge_ref); cudaFree(g.ref_tile_edges);
+	}
+};
+
 } // namespace v2m
+
+struct v2m_graph_s : v2m::graph_holder {};

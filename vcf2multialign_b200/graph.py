@@ -121,6 +121,18 @@ class DeviceGraph:
         check(lib().v2m_cuda_plan_founders(self._h, ptr(cuts), cuts.size - 1, ptr(flat), m.shape[1], C.byref(p)))
         return Plan(self, p)
 
+    def find_matchings(self, cut_positions, founder_count: int, keep_ref_edges: bool = False):
+        """founder_sequence_greedy_output::find_matchings: K3 + host greedy inside the library. Returns the segments × founders
+        matrix of assigned chromosome copies (logical indexing), or None where the reference returns false."""
+        cuts = np.ascontiguousarray(cut_positions, dtype=np.uint64)
+        n_seg = max(cuts.size - 1, 0)
+        assigned = np.full(max(n_seg * founder_count, 1), PLOIDY_MAX, np.uint32)
+        found = C.c_int(0)
+        check(lib().v2m_cuda_find_matchings(self._h, ptr(cuts), cuts.size, founder_count, int(keep_ref_edges), ptr(assigned), C.byref(found)))
+        if not found.value:
+            return None
+        return assigned[: n_seg * founder_count].reshape(founder_count, n_seg).T.copy()
+
     def segment_classes(self, cut_positions, want_rhs_eq: bool = True):
         """K3: per-cut class data for find_matchings. Returns a list (one entry per cut ≥ 1) of dicts with
         distinct, first_class, first_is_ref, rhs_eq (or None) and joined (k × 3: lhs_rep, rhs_rep, size; permutation order)."""

@@ -3,7 +3,7 @@
     transpose_matrix                  include/vcf2multialign/transpose_matrix.hh:14
     output_delegate                   include/vcf2multialign/output.hh:26-38
     haplotype_output                  include/vcf2multialign/output.hh:71-78, libvcf2multialign/haplotype_output.cc
-    founder_sequence_greedy_output    include/vcf2multialign/output.hh:81-130 (output side; matching: see founders.py)
+    founder_sequence_greedy_output    include/vcf2multialign/output.hh:81-130, libvcf2multialign/founder_sequence_greedy_output.cc
 
 Same names, argument meaning and error behaviour (dst files are created exclusively, output.cc:41 / file_handling.cc:81-94).
 The authoritative drop-in is the C++ adapter layer in vcf2multialign_b200/host/; this module exists so that the parity
@@ -146,3 +146,45 @@ class haplotype_output(output):
                 rows.append((self._a2m_id(f"{name}-{1 + c}"), f"{name}.{1 + c}",
                              (lambda name=name, s=s, c=c: d.will_handle_sample(name, s, c)), after))
         return dgraph.plan_haplotypes(np.array(copy_idx, np.uint32)), rows
+
+
+class founder_sequence_greedy_output(output):
+    """output.hh:81-130. find_cut_positions (find_cut_positions.cc:93-211) is SURVEY §8 row f1 ("next"): until it lands, cut
+    positions are supplied the way --input-cut-positions supplies them (load_cut_positions / set_cut_positions)."""
+
+    def __init__(self, chromosome_id, should_output_reference: bool, should_keep_ref_edges: bool, should_output_unaligned: bool,
+                 delegate: output_delegate | None = None):
+        super().__init__(chromosome_id, should_output_reference, should_output_unaligned, delegate)
+        self.m_should_keep_ref_edges = bool(should_keep_ref_edges)
+        self.m_cut_positions = np.zeros(0, np.uint64)
+        self.m_assigned_samples = None                    # segments × founders (logical indexing)
+
+    def cut_positions(self):
+        return self.m_cut_positions
+
+    def set_cut_positions(self, cuts):
+        self.m_cut_positions = np.ascontiguousarray(cuts, dtype=np.uint64)
+
+    def assigned_samples(self):
+        return self.m_assigned_samples
+
+    def find_matchings(self, graph, founder_count: int, ref_seq=None) -> bool:
+        """founder_sequence_greedy_output.cc:154-512. `graph`: DeviceGraph, or VariantGraph + ref_seq."""
+        dgraph = graph if isinstance(graph, DeviceGraph) else DeviceGraph(graph, ref_seq)
+        m = dgraph.find_matchings(self.m_cut_positions, founder_count, self.m_should_keep_ref_edges)
+        if m is None:
+            return False
+        self.m_assigned_samples = m
+        return True
+
+    def _rows(self, dgraph: DeviceGraph):
+        d = self.m_delegate
+        m = self.m_assigned_samples
+        n_founders = m.shape[1]
+        rows = [(self._a2m_id(str(1 + f)), str(1 + f), (lambda f=f: d.will_handle_founder_sequence(f)), (lambda f=f: d.handled_sequences(2 + f)))
+                for f in range(n_founders)]
+        if self.m_should_output_reference:
+            # The REF row goes first (founder_…cc:519-531): a founder column assigned PLOIDY_MAX everywhere follows REF edges only.
+            m = np.concatenate([np.full((m.shape[0], 1), PLOIDY_MAX, np.uint32), m], axis=1)
+            rows = [(self._a2m_id("REF"), "REF", None, lambda: d.handled_sequences(1))] + rows
+        return dgraph.plan_founders(self.m_cut_positions, m), rows
