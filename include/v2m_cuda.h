@@ -178,6 +178,10 @@ int v2m_cuda_synth_paths(void *d_dst, uint64_t h_pad, uint64_t e_pad, uint32_t H
  * measured with CUDA events on the launching stream. */
 int v2m_cuda_time_emit_rows(v2m_plan_t p, uint32_t row_begin, uint32_t row_end, void *d_out, uint64_t pitch,
                             int iters, float *ms_mean);
+/* Device times (CUDA events) of the three K3 passes of the calling thread's last v2m_cuda_segment_classes /
+ * v2m_cuda_find_matchings call: ms3 = {local sweep, boundary composition, per-cut emission};
+ * counts4 = {chunks, cut positions, ALT edges, joined triples}. */
+int v2m_cuda_last_segment_classes_timing(float *ms3, uint64_t *counts4);
 int v2m_cuda_time_transpose_bits(const void *d_src, uint64_t rows, uint64_t cols, void *d_dst, int iters, float *ms_mean);
 
 #ifdef __cplusplus

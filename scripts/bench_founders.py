@@ -1,0 +1,150 @@
+#!/usr/bin/env python3
+"""Config 3 timing (chr22-shaped synthetic, --founder-sequences=25 --minimum-distance=50): K3 passes, find_matchings, founder rows.
+
+    python scripts/bench_founders.py [--workload c2] [--founders 25] [--min-distance 50] [--cpu-edges 3000]
+
+Cut positions: find_initial_cut_positions_lambda_min is SURVEY §8 row f1 ("next") and its CPU form needs E·H std::map
+operations (≈ 5.5e9 on this shape), so the bench supplies cut positions the way --input-cut-positions would: every node
+that no ALT edge spans is a candidate (find_cut_positions.cc:126-129), taken greedily at >= min-distance aligned columns
+with at least one new ALT edge per segment. The CPU baseline is the oracle's find_matchings sweep on a prefix of the same
+graph (first --cpu-edges ALT edges), scaled per edge column.
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes as C
+import json
+import os
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+
+def greedy_cuts(g, min_distance):
+    N = g.node_count()
+    csum = g.alt_edge_count_csum
+    aln = g.aligned_positions
+    tgt = g.alt_edge_targets
+    # rightmost target seen so far, per node (exclusive of the node's own edges)
+    reach = np.zeros(N, np.uint64)
+    src = np.repeat(np.arange(N, dtype=np.int64), np.diff(csum).astype(np.int64))
+    per_node = np.zeros(N, np.uint64)
+    np.maximum.at(per_node, src, tgt)
+    reach[1:] = np.maximum.accumulate(per_node)[:-1]
+    ok = reach <= np.arange(N, dtype=np.uint64)
+    cuts = [0]
+    last_aln, last_edge = 0, 0
+    for n in np.nonzero(ok)[0][1:]:
+        if int(csum[n]) > last_edge and int(aln[n]) - last_aln >= min_distance:
+            cuts.append(int(n))
+            last_aln, last_edge = int(aln[n]), int(csum[n])
+    if cuts[-1] != N - 1:
+        if int(csum[N - 1]) > last_edge:
+            cuts.append(N - 1)
+        else:
+            cuts[-1] = N - 1
+    return np.array(cuts, np.uint64)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--workload", default="c2")
+    ap.add_argument("--founders", type=int, default=25)
+    ap.add_argument("--min-distance", type=int, default=50)
+    ap.add_argument("--cpu-edges", type=int, default=3000)
+    ap.add_argument("--iters", type=int, default=3)
+    args = ap.parse_args()
+
+    import vcf2multialign_b200 as v2m
+    from vcf2multialign_b200 import synth
+    from vcf2multialign_b200._lib import check, lib, ptr
+    L = lib()
+    check(L.v2m_cuda_init(0))
+    w = synth.make_workload(args.workload, seed=1, with_paths=False)
+    g = w.graph
+    H, A, E = g.total_chromosome_copies(), g.aligned_length(), g.edge_count()
+    path_bytes = g.e_pad * g.h_pad // 8
+    d_paths = L.v2m_cuda_device_alloc(path_bytes)
+    synth.path_bits_device(w, d_paths)
+    dg = v2m.DeviceGraph(g, w.ref, d_paths_by_edge_and_chrom_copy=d_paths)
+    cuts = greedy_cuts(g, args.min_distance)
+    n_seg = cuts.size - 1
+
+    out = {"workload": f"{args.workload}: {E} ALT edges x {H} chromosome copies, {cuts.size} cut positions (min distance {args.min_distance}), {args.founders} founders"}
+    # K3 + greedy
+    best = None
+    for _ in range(args.iters):
+        t0 = time.perf_counter()
+        m = dg.find_matchings(cuts, args.founders)
+        dt = time.perf_counter() - t0
+        ms = (C.c_float * 3)()
+        cnt = (C.c_uint64 * 4)()
+        L.v2m_cuda_last_segment_classes_timing(ms, cnt)
+        rec = {"find_matchings_s": dt, "k3_local_ms": ms[0], "k3_compose_ms": ms[1], "k3_emit_ms": ms[2], "chunks": int(cnt[0]), "joined_triples": int(cnt[3])}
+        if best is None or dt < best["find_matchings_s"]:
+            best = rec
+    out.update(best)
+    k3_ms = best["k3_local_ms"] + best["k3_compose_ms"] + best["k3_emit_ms"]
+    out["k3_total_ms"] = k3_ms
+    out["k3_us_per_edge_column_per_chunk"] = 1e3 * (best["k3_local_ms"]) / (E / max(best["chunks"], 1))
+    out["k3_path_matrix_gbs"] = 2 * path_bytes / (k3_ms * 1e-3) / 1e9
+
+    # founder rows (K2c + K2a + K2b), device resident
+    assigned = m
+    t0 = time.perf_counter()
+    plan = dg.plan_founders(cuts, np.concatenate([np.full((n_seg, 1), v2m.PLOIDY_MAX, np.uint32), assigned], axis=1))
+    out["plan_founders_s"] = time.perf_counter() - t0
+    n_rows = plan.row_count()
+    pitch = (A + 15) // 16 * 16
+    d_out = L.v2m_cuda_device_alloc(n_rows * pitch)
+    ms1 = C.c_float()
+    check(L.v2m_cuda_time_emit_rows(plan._p, 0, n_rows, d_out, pitch, 1, C.byref(ms1)))
+    check(L.v2m_cuda_time_emit_rows(plan._p, 0, n_rows, d_out, pitch, 5, C.byref(ms1)))
+    out["founder_rows"] = n_rows
+    out["founder_rows_emit_ms"] = ms1.value
+    out["founder_rows_gbase_per_s"] = n_rows * A / (ms1.value * 1e-3) / 1e9
+    # spot check: founder row 1, first segments, equals the assigned haplotype's row there
+    hp = dg.plan_haplotypes(np.array([assigned[0, 0]], np.uint32))
+    c1 = int(g.aligned_positions[int(cuts[1])])
+    assert np.array_equal(plan.emit_rows(1, 2, 0, c1), hp.emit_rows(0, 1, 0, c1))
+
+    # CPU: oracle sweep on a prefix of the graph
+    if args.cpu_edges > 0:
+        from oracle import oracle as orc
+        n_cut_cpu = int(np.searchsorted(g.alt_edge_count_csum[cuts.astype(np.int64)], args.cpu_edges))
+        n_cut_cpu = max(2, min(n_cut_cpu, cuts.size - 1))
+        last_node = int(cuts[n_cut_cpu])
+        e_cpu = int(g.alt_edge_count_csum[last_node])
+        e_pad = (e_cpu + 63) // 64 * 64
+        Wh = g.h_pad // 64
+        words = np.zeros(path_bytes // 8, np.uint64)
+        check(L.v2m_cuda_memcpy_d2h(ptr(words), d_paths, path_bytes))
+        sub = np.zeros(e_pad * Wh, np.uint64)
+        sub[: e_cpu * Wh] = words[: e_cpu * Wh]
+        del words
+        N2 = last_node + 1
+        og = orc.Graph.from_arrays(dict(
+            reference_positions=g.reference_positions[:N2], aligned_positions=g.aligned_positions[:N2], alt_edge_targets=g.alt_edge_targets[:e_cpu],
+            alt_edge_count_csum=np.concatenate([g.alt_edge_count_csum[:N2], [e_cpu]]).astype(np.uint64), label_offsets=g.label_offsets[: e_cpu + 1],
+            label_chars=g.label_chars[: int(g.label_offsets[e_cpu])], paths_ec=sub, paths_ce=None, h_pad=g.h_pad, e_pad=e_pad,
+            ploidy_csum=g.ploidy_csum, sample_names=g.sample_names, ref=w.ref[: int(g.reference_positions[last_node]) + 1]))
+        f = orc.FounderOutput(og)
+        f.set_cut_positions(cuts[: n_cut_cpu + 1])
+        t0 = time.perf_counter()
+        ok = f.find_matchings(args.founders)
+        t_cpu = time.perf_counter() - t0
+        out["cpu_oracle"] = {"edges": e_cpu, "cuts": n_cut_cpu + 1, "seconds": t_cpu, "us_per_edge_column": 1e6 * t_cpu / e_cpu,
+                             "extrapolated_full_s": t_cpu / e_cpu * E, "ok": bool(ok)}
+        # parity on the prefix: same assignments for the segments both saw (the oracle graph ends at last_node)
+        sub_assigned = f.assigned_samples()
+        assert np.array_equal(sub_assigned[: n_cut_cpu - 1], assigned[: n_cut_cpu - 1]), "GPU and oracle assignments differ on the prefix"
+        out["cpu_oracle"]["prefix_segments_identical"] = int(n_cut_cpu - 1)
+    print(json.dumps(out))
+
+
+if __name__ == "__main__":
+    main()

@@ -75,6 +75,7 @@ SYMBOLS = {
     "v2m_cuda_write_a2m": (_i32, [_vp, C.c_char_p, _i32, _i32, ROW_CALLBACK, _vp]),
     "v2m_cuda_segment_classes": (_i32, [_vp, _vp, _u64, _vp, _vp, _vp, _vp, _vp, _vp, _u64]),
     "v2m_cuda_find_matchings": (_i32, [_vp, _vp, _u64, _u32, _i32, _vp, _vp]),
+    "v2m_cuda_last_segment_classes_timing": (_i32, [_vp, _vp]),
     "v2m_cuda_synth_paths": (_i32, [_vp, _u64, _u64, _u32, _u64, _u32, _vp, _vp, _vp]),
     "v2m_cuda_time_emit_rows": (_i32, [_vp, _u32, _u32, _vp, _u64, _i32, _vp]),
     "v2m_cuda_time_transpose_bits": (_i32, [_vp, _u64, _u64, _vp, _i32, _vp]),

@@ -611,6 +611,9 @@ namespace {
 	}
 }
 
+struct k3_timing { float ms_local{}, ms_compose{}, ms_emit{}; u64 n_chunks{}, n_cuts{}, n_edges{}, joined_triples{}; };
+k3_timing &last_k3_timing() { thread_local k3_timing t; return t; }
+
 // Results of K3 on the host, in the layout of v2m_cuda_segment_classes.
 int segment_classes_host(graph_holder const &gh, u64 const *cut_positions, u64 const n_cuts, bool const want_rhs_eq, int const max_chunks,
 	std::vector<u32> &rhs_eq, std::vector<u32> &distinct, std::vector<u32> &first_class, std::vector<u8> &first_is_ref,
@@ -684,9 +687,15 @@ int segment_classes_host(graph_holder const &gh, u64 const *cut_positions, u64 c
 	kp.distinct = d_distinct.as<u32>(); kp.first_class = d_first.as<u32>(); kp.first_is_ref = d_isref.as<u8>(); kp.joined_count = d_jcount.as<u32>();
 	kp.joined_base = d_jbase.as<u64>();
 
+	cudaEvent_t ev[4];
+	for (auto &e : ev) V2M_CUDA_TRY(cudaEventCreate(&e));
+	struct ev_guard { cudaEvent_t *e; ~ev_guard() { for (int i(0); i < 4; ++i) cudaEventDestroy(e[i]); } } const guard{ev};
+	cudaEventRecord(ev[0], nullptr);
 	if (n_chunks > 1)
 		if (int const st = k3_dispatch(KW, 0, kp, n_chunks - 1, smem, nullptr)) return st;
+	cudaEventRecord(ev[1], nullptr);
 	if (int const st = k3_dispatch(KW, 1, kp, 1, smem, nullptr)) return st;
+	cudaEventRecord(ev[2], nullptr);
 
 	// Joined triples go to per-chunk regions of a pool; a first guess of 48 per cut + H per chunk, exact sizes on a retry.
 	std::vector<u64> jbase(n_chunks + 1, 0);
@@ -698,7 +707,9 @@ int segment_classes_host(graph_holder const &gh, u64 const *cut_positions, u64 c
 		if (d_joined.alloc(jbase[n_chunks] * 12)) return V2M_ERR_CUDA;
 		kp.joined = d_joined.as<u32>();
 		V2M_CUDA_TRY(cudaMemcpy(d_jbase.p, jbase.data(), jbase.size() * 8, cudaMemcpyHostToDevice));
+		if (attempt) cudaEventRecord(ev[2], nullptr);
 		if (int const st = k3_dispatch(KW, 2, kp, n_chunks, smem, nullptr)) return st;
+		cudaEventRecord(ev[3], nullptr);
 		V2M_CUDA_TRY(cudaMemcpy(jcount.data(), d_jcount.p, n_seg * 4, cudaMemcpyDeviceToHost));
 		bool fits(true);
 		std::vector<u64> need(n_chunks + 1, 0);
@@ -731,11 +742,27 @@ int segment_classes_host(graph_holder const &gh, u64 const *cut_positions, u64 c
 		V2M_CUDA_TRY(cudaMemcpy(rhs_eq.data(), d_rhs.p, n_seg * g.H * 4, cudaMemcpyDeviceToHost));
 	}
 	V2M_CUDA_TRY(cudaDeviceSynchronize());
+	{
+		k3_timing &t(last_k3_timing());
+		t = k3_timing{};
+		cudaEventElapsedTime(&t.ms_local, ev[0], ev[1]);
+		cudaEventElapsedTime(&t.ms_compose, ev[1], ev[2]);
+		cudaEventElapsedTime(&t.ms_emit, ev[2], ev[3]);
+		t.n_chunks = n_chunks; t.n_cuts = n_cuts; t.n_edges = g.E; t.joined_triples = joined_offsets[n_seg];
+	}
 	return V2M_OK;
 }
 
 } // namespace v2m
 
+
+extern "C" int v2m_cuda_last_segment_classes_timing(float *ms3, uint64_t *counts4)
+{
+	v2m::k3_timing const &t(v2m::last_k3_timing());
+	if (ms3) { ms3[0] = t.ms_local; ms3[1] = t.ms_compose; ms3[2] = t.ms_emit; }
+	if (counts4) { counts4[0] = t.n_chunks; counts4[1] = t.n_cuts; counts4[2] = t.n_edges; counts4[3] = t.joined_triples; }
+	return V2M_OK;
+}
 
 extern "C" int v2m_cuda_segment_classes(v2m_graph_t g, const uint64_t *cut_positions, uint64_t n_cuts,
 	uint32_t *rhs_eq, uint32_t *distinct, uint32_t *first_class, uint8_t *first_is_ref,
