@@ -140,6 +140,10 @@ int v2m_cuda_emit_rows_unaligned(v2m_plan_t p, uint32_t row_begin, uint32_t row_
  * from the calling thread after each row has been handed to write(2) — the hook behind output_delegate::handled_sequences. */
 typedef void (*v2m_row_callback)(uint32_t row, void *ctx);
 int v2m_cuda_write_a2m(v2m_plan_t p, const char *ids, int unaligned, int fd, v2m_row_callback row_done, void *ctx);
+/* The same stream handed to a caller-supplied sink (e.g. an std::ostream behind the C++ adapter, or the stdin of a --pipe
+ * subprocess, output.cc:49-67). The sink returns 0 on success; anything else aborts the stream with V2M_ERR_STATE. */
+typedef int (*v2m_sink)(const void *bytes, uint64_t n, void *ctx);
+int v2m_cuda_stream_a2m(v2m_plan_t p, const char *ids, int unaligned, v2m_sink sink, void *sink_ctx, v2m_row_callback row_done, void *ctx);
 
 /* --- K3: per-cut haplotype classes for founder_sequence_greedy_output::find_matchings
  *         (libvcf2multialign/founder_sequence_greedy_output.cc:213-253, 460-469; pbwt.hh:77-134) ----------- */

@@ -427,3 +427,22 @@ def test_find_matchings_degenerate(v2m, golden_dir):
         dg.segment_classes([0, 2, 2, N - 1])                    # cut positions must increase
     with pytest.raises(v2m.V2MError):
         dg.segment_classes([1, N - 1])                          # first cut must be node 0
+
+
+# ---- C++ host adapters (vcf2multialign_b200/host/v2m_b200.hh) ------------------------------------------------------------
+@pytest.mark.parametrize("fa,vcf", [("founder-sequences/test-1.fa", "founder-sequences/test-1.vcf"), ("founder-sequences/test-1-2.fa", "founder-sequences/test-1.vcf"),
+                                    ("founder-sequences/test-2.fa", "founder-sequences/test-2.vcf"), ("founder-sequences/test-3.fa", "founder-sequences/test-3.vcf"),
+                                    ("founder-sequences/test-4.fa", "founder-sequences/test-4.vcf"), ("variant-graph/test-2.fa", "variant-graph/test-2.vcf"),
+                                    ("variant-graph/test-4.fa", "variant-graph/test-4.vcf")])
+def test_cxx_host_adapters(v2m, expected, golden_dir, tmp_path, fa, vcf):
+    """transpose_matrix, output_sequence, haplotype_output, founder_sequence_greedy_output with the reference's signatures,
+    byte-compared with the oracle inside tests/host/adapter_test.cc (incl. delegate call order, O_EXCL, --pipe, output_separate)."""
+    import subprocess
+    exe = os.path.join(os.path.dirname(__file__), "host", "_build", "adapter_test")
+    if not os.path.exists(exe):
+        subprocess.run(["make", "-C", os.path.join(os.path.dirname(__file__), "host")], check=True)
+    r = subprocess.run([exe, os.path.join(golden_dir, fa), os.path.join(golden_dir, vcf), str(tmp_path), "2"], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and "ALL OK" in r.stdout, r.stdout[-3000:] + r.stderr[-2000:]
+    if fa.startswith("founder-sequences"):
+        case = [c for c in expected["founder_sequences"] if c["vcf"] == os.path.basename(vcf) and c["fa"] == os.path.basename(fa)]
+        assert case and case[0]["a2m"] in r.stdout      # the founder A2M text the test program echoes is the reference's golden

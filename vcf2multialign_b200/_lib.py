@@ -37,6 +37,7 @@ class GraphView(C.Structure):
 
 
 ROW_CALLBACK = C.CFUNCTYPE(None, C.c_uint32, C.c_void_p)
+SINK = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_uint64, C.c_void_p)
 
 # name → (restype, argtypes); every symbol include/v2m_cuda.h declares.
 _vp, _u64, _u32, _i32 = C.c_void_p, C.c_uint64, C.c_uint32, C.c_int
@@ -73,6 +74,7 @@ SYMBOLS = {
     "v2m_cuda_emit_rows": (_i32, [_vp, _u32, _u32, _u64, _u64, _vp, _u64]),
     "v2m_cuda_emit_rows_unaligned": (_i32, [_vp, _u32, _u32, _vp, _vp]),
     "v2m_cuda_write_a2m": (_i32, [_vp, C.c_char_p, _i32, _i32, ROW_CALLBACK, _vp]),
+    "v2m_cuda_stream_a2m": (_i32, [_vp, C.c_char_p, _i32, SINK, _vp, ROW_CALLBACK, _vp]),
     "v2m_cuda_segment_classes": (_i32, [_vp, _vp, _u64, _vp, _vp, _vp, _vp, _vp, _vp, _u64]),
     "v2m_cuda_find_matchings": (_i32, [_vp, _vp, _u64, _u32, _i32, _vp, _vp]),
     "v2m_cuda_last_segment_classes_timing": (_i32, [_vp, _vp]),

@@ -588,9 +588,16 @@ namespace {
 	}
 }
 
+static int fd_sink(const void *bytes, uint64_t n, void *ctx) { return write_all(*static_cast<int *>(ctx), bytes, size_t(n)); }
+
 extern "C" int v2m_cuda_write_a2m(v2m_plan_t p, const char *ids, int unaligned, int fd, v2m_row_callback row_done, void *ctx)
 {
-	if (!p || (!ids && p->p.n_rows)) return fail(V2M_ERR_ARGUMENT, "write_a2m: NULL argument");
+	return v2m_cuda_stream_a2m(p, ids, unaligned, fd_sink, &fd, row_done, ctx);
+}
+
+extern "C" int v2m_cuda_stream_a2m(v2m_plan_t p, const char *ids, int unaligned, v2m_sink sink, void *sink_ctx, v2m_row_callback row_done, void *ctx)
+{
+	if (!p || !sink || (!ids && p->p.n_rows)) return fail(V2M_ERR_ARGUMENT, "stream_a2m: NULL argument");
 	device_graph const &g(*p->p.graph);
 	u32 const n_rows(p->p.n_rows);
 	if (0 == n_rows) return V2M_OK;
@@ -647,9 +654,14 @@ extern "C" int v2m_cuda_write_a2m(v2m_plan_t p, const char *ids, int unaligned, 
 				std::string header(">");
 				header += id; header += '\n';
 				id += std::strlen(id) + 1;
-				if ((st = write_all(fd, header.data(), header.size()))) break;
-				if ((st = write_all(fd, h_buf[k] + u64(r - r0) * pitch, lengths[r]))) break;
-				if ((st = write_all(fd, "\n", 1))) break;
+				auto const put([&](void const *bytes, u64 n) -> int {
+					int const rc(sink(bytes, n, sink_ctx));
+					if (rc && sink != fd_sink) fail(V2M_ERR_STATE, "stream_a2m: the sink reported an error");
+					return rc ? V2M_ERR_STATE : V2M_OK;
+				});
+				if ((st = put(header.data(), header.size()))) break;
+				if ((st = put(h_buf[k] + u64(r - r0) * pitch, lengths[r]))) break;
+				if ((st = put("\n", 1))) break;
 				if (row_done) row_done(r, ctx);
 			}
 		}
