@@ -446,3 +446,32 @@ def test_cxx_host_adapters(v2m, expected, golden_dir, tmp_path, fa, vcf):
     if fa.startswith("founder-sequences"):
         case = [c for c in expected["founder_sequences"] if c["vcf"] == os.path.basename(vcf) and c["fa"] == os.path.basename(fa)]
         assert case and case[0]["a2m"] in r.stdout      # the founder A2M text the test program echoes is the reference's golden
+
+
+# ---- row-range sharding with the GPU as the row producer ------------------------------------------------------------
+@pytest.mark.parametrize("unaligned", [False, True])
+def test_sharded_stream_gpu_rows(v2m, tmp_path, unaligned):
+    """Three 'ranks' (run one after the other in this process, no collective needed) each write their row range."""
+    from vcf2multialign_b200 import sharding
+    og = rg.random_oracle_graph(str(tmp_path), 4242, ref_len=5000, n_records=500, n_samples=7, ploidy=2, long_del_prob=0.02)
+    dg, g = _device_graph(v2m, og)
+    out = v2m.haplotype_output("c", True, unaligned)
+    dst = str(tmp_path / "sharded.a2m")
+    world = 3
+    if unaligned:
+        # every rank needs all lengths: without a process group, hand them over as gather_lengths would
+        plan = dg.plan_haplotypes(np.array(out._row_table(g)[0], np.uint32))
+        all_lengths = plan.row_lengths(True)
+
+        class FakeDist:
+            def barrier(self): pass
+            def all_gather_object(self, parts, local):
+                for r in range(world):
+                    b, e = sharding.row_range(len(all_lengths), r, world)
+                    parts[r] = [int(x) for x in all_lengths[b:e]]
+        dist = FakeDist()
+    else:
+        dist = None
+    for rank in range(world):
+        sharding.sharded_haplotype_output_a2m(out, g, dg, dst, rank, world, dist, block_rows=4)
+    assert open(dst, "rb").read() == og.haplotype_output_a2m("c", True, unaligned)

@@ -126,25 +126,25 @@ class output:
 
 
 class haplotype_output(output):
-    def _rows(self, dgraph: DeviceGraph):
-        g: VariantGraph = dgraph.graph
+    def _row_table(self, g: VariantGraph):
+        """→ (chromosome copy index per row, [(a2m id, separate-file stem, before-hook, after-hook)…]); no device involved."""
         d = self.m_delegate
         copy_idx, rows = [], []
-        seq_count = [1]                                  # haplotype_output.cc:46: starts at 1 even with --omit-reference
-
         if self.m_should_output_reference:
             copy_idx.append(PLOIDY_MAX)
             rows.append((self._a2m_id("REF"), "REF", None, lambda: d.handled_sequences(1)))
-
-        def after():
-            seq_count[0] += 1
-            d.handled_sequences(seq_count[0])
-
+        k = 0
         for s, name in enumerate(g.sample_names):
             for c in range(g.sample_ploidy(s)):
                 copy_idx.append(int(g.ploidy_csum[s]) + c)
+                # haplotype_output.cc:46, 78-79: seq_count starts at 1 even with --omit-reference, so the k-th sample row reports k + 2
                 rows.append((self._a2m_id(f"{name}-{1 + c}"), f"{name}.{1 + c}",
-                             (lambda name=name, s=s, c=c: d.will_handle_sample(name, s, c)), after))
+                             (lambda name=name, s=s, c=c: d.will_handle_sample(name, s, c)), (lambda k=k: d.handled_sequences(k + 2))))
+                k += 1
+        return copy_idx, rows
+
+    def _rows(self, dgraph: DeviceGraph):
+        copy_idx, rows = self._row_table(dgraph.graph)
         return dgraph.plan_haplotypes(np.array(copy_idx, np.uint32)), rows
 
 

@@ -1,0 +1,141 @@
+"""Row-range sharding of one A2M stream over the GPUs of a box: rows are independent, so rank r owns a
+contiguous range of the output rows, produces them on its own GPU and writes them at their final byte offsets of the
+shared output file with pwrite(2). No data-path collective: the only exchange is the control-plane barrier after rank 0
+has created the file (and, for --unaligned, an all-gather of the per-row lengths — a few KB).
+
+The byte layout is the one haplotype_output::output_a2m produces (haplotype_output.cc:38-82): '>' id '\\n' row '\\n' per row.
+"""
+from __future__ import annotations
+
+import os
+
+import numpy as np
+
+
+def row_range(n_rows: int, rank: int, world: int) -> tuple[int, int]:
+    """Contiguous, balanced: the first n_rows % world ranks get one row more."""
+    if world < 1 or not 0 <= rank < world:
+        raise ValueError("rank / world out of range")
+    base, extra = divmod(n_rows, world)
+    begin = rank * base + min(rank, extra)
+    return begin, begin + base + (1 if rank < extra else 0)
+
+
+def row_offsets(ids, lengths) -> np.ndarray:
+    """Byte offset of every row's '>' in the stream, plus the total size as the last entry."""
+    sizes = np.array([1 + len(i.encode()) + 1 + int(n) + 1 for i, n in zip(ids, lengths)], np.int64)
+    out = np.zeros(len(sizes) + 1, np.int64)
+    np.cumsum(sizes, out=out[1:])
+    return out
+
+
+def _pwrite_all(fd: int, data, offset: int):
+    view = memoryview(data)
+    while len(view):
+        n = os.pwrite(fd, view, offset)
+        view = view[n:]
+        offset += n
+
+
+class ShardedA2MWriter:
+    """Writes this rank's rows of an A2M stream into the shared file `path`.
+
+    ids: the FASTA identifiers of ALL rows (every rank computes the same list from the graph);
+    lengths: byte length of every row (aligned: all equal to aligned_positions.back());
+    dist: an initialised torch.distributed module (any backend) or None for a single process."""
+
+    def __init__(self, path: str, ids, lengths, rank: int = 0, world: int = 1, dist=None):
+        if len(ids) != len(lengths):
+            raise ValueError("ids and lengths differ in length")
+        self.path, self.ids, self.rank, self.world, self.dist = path, list(ids), rank, world, dist
+        self.lengths = [int(x) for x in lengths]
+        self.offsets = row_offsets(self.ids, self.lengths)
+        self.begin, self.end = row_range(len(self.ids), rank, world)
+        self.fd = None
+
+    def __enter__(self):
+        if self.rank == 0:
+            # exclusive create, as lb::open_file_for_writing(…, CREATE) does (output.cc:70)
+            fd = os.open(self.path, os.O_WRONLY | os.O_CREAT | os.O_EXCL, 0o644)
+            os.ftruncate(fd, int(self.offsets[-1]))
+            self.fd = fd
+        if self.dist is not None and self.world > 1:
+            self.dist.barrier()
+        if self.rank != 0:
+            self.fd = os.open(self.path, os.O_WRONLY)
+        return self
+
+    def write_rows(self, first_row: int, rows):
+        """rows: iterable of bytes-like row bodies for rows first_row, first_row + 1, … (all within this rank's range)."""
+        r = first_row
+        for body in rows:
+            if not self.begin <= r < self.end:
+                raise ValueError(f"row {r} is outside rank {self.rank}'s range [{self.begin}, {self.end})")
+            if len(body) != self.lengths[r]:
+                raise ValueError(f"row {r}: {len(body)} bytes, expected {self.lengths[r]}")
+            head = b">" + self.ids[r].encode() + b"\n"
+            off = int(self.offsets[r])
+            _pwrite_all(self.fd, head, off)
+            _pwrite_all(self.fd, body, off + len(head))
+            _pwrite_all(self.fd, b"\n", off + len(head) + len(body))
+            r += 1
+
+    def __exit__(self, *exc):
+        if self.fd is not None:
+            os.close(self.fd)
+            self.fd = None
+        if self.dist is not None and self.world > 1 and exc[0] is None:
+            self.dist.barrier()
+        return False
+
+
+def gather_lengths(local_lengths, n_rows: int, rank: int, world: int, dist=None) -> list[int]:
+    """--unaligned: every rank knows only its own rows' lengths; all-gather them (control plane, 8 bytes per row)."""
+    begin, end = row_range(n_rows, rank, world)
+    if len(local_lengths) != end - begin:
+        raise ValueError("local_lengths does not match this rank's row range")
+    if dist is None or world == 1:
+        return [int(x) for x in local_lengths]
+    parts = [None] * world
+    dist.all_gather_object(parts, [int(x) for x in local_lengths])
+    return [x for p in parts for x in p]
+
+
+def sharded_haplotype_output_a2m(out, graph, dgraph, path: str, rank: int = 0, world: int = 1, dist=None, block_rows: int = 64, row_source=None):
+    """haplotype_output::output_a2m over `world` GPUs. `out`: vcf2multialign_b200.output.haplotype_output; `graph`: the
+    VariantGraph; `dgraph`: this rank's DeviceGraph (None only when row_source is given). row_source — an object with
+    lengths(copy_idx, unaligned) and rows(copy_idx, unaligned) — replaces the GPU producer in the CPU (gloo) tests."""
+    plan_idx, rows = out._row_table(graph)
+    n = len(rows)
+    begin, end = row_range(n, rank, world)
+    ids = [r[0] for r in rows]
+    unaligned = out.m_should_output_unaligned
+    plan = None
+    if row_source is None:
+        plan = dgraph.plan_haplotypes(np.asarray(plan_idx[begin:end], np.uint32))
+    try:
+        if unaligned:
+            local = plan.row_lengths(True) if plan is not None else row_source.lengths(plan_idx[begin:end], True)
+            lengths = gather_lengths(local, n, rank, world, dist)
+        else:
+            lengths = [graph.aligned_length()] * n
+        with ShardedA2MWriter(path, ids, lengths, rank, world, dist) as w:
+            for r0 in range(begin, end, block_rows):
+                r1 = min(end, r0 + block_rows)
+                if plan is None:
+                    bodies = row_source.rows(plan_idx[r0:r1], unaligned)
+                elif unaligned:
+                    bodies = plan.emit_rows_unaligned(r0 - begin, r1 - begin)
+                else:
+                    arr = plan.emit_rows(r0 - begin, r1 - begin)
+                    bodies = [arr[i] for i in range(r1 - r0)]
+                for r in range(r0, r1):
+                    if rows[r][2]:
+                        rows[r][2]()
+                w.write_rows(r0, bodies)
+                for r in range(r0, r1):
+                    if rows[r][3]:
+                        rows[r][3]()
+    finally:
+        if plan is not None:
+            plan.close()
