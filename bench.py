@@ -248,7 +248,9 @@ def main():
     traffic = None
     try:
         with open(os.path.join(ROOT, "profiles", "emit_rows_traffic.json")) as f:
-            traffic = json.load(f).get("dram_bytes_per_launch")
+            tj = json.load(f)
+            if tj.get("workload") == args.workload and tj.get("rows_per_launch") == min(block, n_rows):
+                traffic = tj.get("dram_bytes_per_launch")
     except Exception:
         pass
     roofline = {"bound": "hbm", "kernel": "emit_rows_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
