@@ -171,6 +171,22 @@ int v2m_cuda_segment_classes(v2m_graph_t g, const uint64_t *cut_positions, uint6
 int v2m_cuda_find_matchings(v2m_graph_t g, const uint64_t *cut_positions, uint64_t n_cuts, uint32_t founder_count,
                             int keep_ref_edges, uint32_t *assigned, int *found);
 
+/* --- K4: founder_sequence_greedy_output::find_cut_positions(graph, minimum_distance) (include/vcf2multialign/output.hh:123,
+ *         libvcf2multialign/founder_sequence_greedy_output.cc:139-152), i.e. find_initial_cut_positions_lambda_min
+ *         (include/vcf2multialign/find_cut_positions.hh:22-27, libvcf2multialign/find_cut_positions.cc:93-211) ------ */
+/* The pBWT sweep and, at every candidate cut position, the (candidate index, equivalence class count) pairs the reference
+ * derives from its divergence value counts run on the device; the recurrence over candidates and the trace-back run on the
+ * host. cut_positions receives *n_cuts node ids (first 0, last the sink, as cut_positions() returns them); *score =
+ * max_segmentation_height() (the CLI prints 1 + score, main.cc:520); *found = what the reference's member returns (0 iff
+ * the score is CUT_POSITION_SCORE_MAX). If cap is too small the call returns V2M_ERR_ARGUMENT with the needed count in
+ * *n_cuts. At most 8192 chromosome copies. */
+int v2m_cuda_find_cut_positions(v2m_graph_t g, uint64_t min_distance, uint64_t *cut_positions, uint64_t cap,
+                                uint64_t *n_cuts, uint32_t *score, int *found);
+/* Timing of the calling thread's last v2m_cuda_find_cut_positions: ms4 = {local sweep, boundary composition, list extraction
+ * (device, CUDA events), whole call (host clock)}; counts6 = {chunks, candidates, ALT edges, list pairs read by the recurrence,
+ * list capacity per candidate, list extraction attempts}. */
+int v2m_cuda_last_cut_positions_timing(float *ms4, uint64_t *counts6);
+
 /* --- synthetic workloads (measurement infrastructure) ------------------------------------------------ */
 /* Fills d_dst (device, e_pad × h_pad/64 words = paths_by_edge_and_chrom_copy) with LD-structured path bits that are a
  * pure function of (seed, chromosome copy, site); per edge: its site, its 0-based ALT number, the site's ALT count. */

@@ -429,6 +429,86 @@ def test_find_matchings_degenerate(v2m, golden_dir):
         dg.segment_classes([1, N - 1])                          # first cut must be node 0
 
 
+# ---- K4: cut positions (find_cut_positions.cc:93-211) --------------------------------------------------------------------
+def _check_cuts(og, dg, min_distance, label=""):
+    f = orc.FounderOutput(og)
+    ok = f.find_cut_positions(min_distance)
+    cuts, score = dg.find_cut_positions(min_distance)
+    if not ok:
+        assert cuts is None, label
+        return None
+    assert cuts is not None, label
+    assert cuts.tolist() == f.cut_positions().tolist(), (label, cuts.tolist(), f.cut_positions().tolist())
+    assert score == f.score(), (label, score, f.score())
+    return cuts
+
+
+def test_cut_positions_on_reference_goldens(v2m, expected, golden_dir):
+    """The cut positions of tests/founder_sequences.cc:118-188 (minimum distance 0), then the whole chain
+    find_cut_positions -> find_matchings -> output_a2m through the reference-shaped mirror."""
+    for case in expected["founder_sequences"]:
+        d = os.path.join(golden_dir, "founder-sequences")
+        og = orc.Graph.from_files(os.path.join(d, case["fa"]), os.path.join(d, case["vcf"]), "1")
+        dg, g = _device_graph(v2m, og)
+        cuts = _check_cuts(og, dg, 0, case["vcf"])
+        assert cuts.tolist() == case["cuts"]
+        out = v2m.founder_sequence_greedy_output(None, True, False, False)
+        assert out.find_cut_positions(dg, 0)
+        assert out.find_matchings(dg, 2)
+        import tempfile
+        with tempfile.TemporaryDirectory() as td:
+            dst = os.path.join(td, "out.a2m")
+            out.output_a2m(None, dg, dst)
+            assert open(dst).read() == case["a2m"], case["vcf"]
+
+
+@pytest.mark.parametrize("chunks,cap", [("1", None), ("2", "1"), ("3", "2"), ("5", "3"), (None, None), (None, "1")])
+def test_cut_positions_random_graphs(v2m, tmp_path, chunks, cap, monkeypatch):
+    """Seeded random graphs (overlapping deletions, multi-allelic sites), several minimum distances; odd chunk counts and tiny
+    list capacities force the chunk-boundary composition, the old-index extraction and the capacity retry."""
+    for name, val in (("V2M_K3_CHUNKS", chunks), ("V2M_K4_CAP", cap)):
+        if val is None:
+            monkeypatch.delenv(name, raising=False)
+        else:
+            monkeypatch.setenv(name, val)
+    for seed in range(14):
+        og = rg.random_oracle_graph(str(tmp_path), 2100 + seed, ref_len=900, n_records=60 + 12 * seed, n_samples=1 + 3 * seed, ploidy=1 + seed % 2,
+                                    overlap=bool(seed % 2), sv=bool(seed % 3), alt_freq=0.1 + 0.03 * seed)
+        dg, g = _device_graph(v2m, og)
+        for md in (0, 7, 40, 400, 5000):
+            _check_cuts(og, dg, md, f"seed {seed} md {md} chunks {chunks} cap {cap}")
+
+
+@pytest.mark.parametrize("n_samples,chunks,cap", [(520, "4", None), (1100, "7", "4"), (2504, None, None)])
+def test_cut_positions_many_copies(v2m, n_samples, chunks, cap, monkeypatch):
+    """KW 2, 3 and the 5,008-copy shape of c3 on LD-structured bits; then find_matchings on the device-made cuts."""
+    from vcf2multialign_b200 import synth
+    for name, val in (("V2M_K3_CHUNKS", chunks), ("V2M_K4_CAP", cap)):
+        if val is None:
+            monkeypatch.delenv(name, raising=False)
+        else:
+            monkeypatch.setenv(name, val)
+    w = synth.make_workload("custom", seed=6, ref_len=120_000, n_sites=2_400, n_samples=n_samples, with_paths=True)
+    g = w.graph
+    og = orc.Graph.from_arrays(dict(
+        reference_positions=g.reference_positions, aligned_positions=g.aligned_positions, alt_edge_targets=g.alt_edge_targets,
+        alt_edge_count_csum=g.alt_edge_count_csum, label_offsets=g.label_offsets, label_chars=g.label_chars,
+        paths_ec=g.paths_by_edge_and_chrom_copy, paths_ce=None, h_pad=g.h_pad, e_pad=g.e_pad, ploidy_csum=g.ploidy_csum,
+        sample_names=g.sample_names, ref=w.ref))
+    dg = v2m.DeviceGraph(g, w.ref)
+    for md in (0, 50, 1000):
+        cuts = _check_cuts(og, dg, md, f"synth {n_samples} md {md}")
+        assert cuts is not None
+
+
+def test_cut_positions_degenerate(v2m, tmp_path):
+    """No ALT edges at all: the only candidate is node 0 and the result is the sink alone (find_cut_positions.cc:199-207)."""
+    og = rg.random_oracle_graph(str(tmp_path), 77, ref_len=200, n_records=12, n_samples=3, ploidy=2, alt_freq=0.0)
+    dg, g = _device_graph(v2m, og)
+    _check_cuts(og, dg, 0, "no edges")
+    _check_cuts(og, dg, 10, "no edges md 10")
+
+
 # ---- C++ host adapters (vcf2multialign_b200/host/v2m_b200.hh) ------------------------------------------------------------
 @pytest.mark.parametrize("fa,vcf", [("founder-sequences/test-1.fa", "founder-sequences/test-1.vcf"), ("founder-sequences/test-1-2.fa", "founder-sequences/test-1.vcf"),
                                     ("founder-sequences/test-2.fa", "founder-sequences/test-2.vcf"), ("founder-sequences/test-3.fa", "founder-sequences/test-3.vcf"),

@@ -185,6 +185,8 @@ int v2m_cuda_graph_upload(const v2m_graph_view *view, v2m_graph_t *out)
 	g.n_tiles = (A + K2_TCOL - 1) / K2_TCOL;
 	g.A_alloc = std::max<u64>(g.n_tiles, 1) * K2_TCOL;
 	holder->csum.assign(view->alt_edge_count_csum, view->alt_edge_count_csum + N + 1);
+	holder->alnpos.assign(view->aligned_positions, view->aligned_positions + N);
+	if (E) holder->targets.assign(view->alt_edge_targets, view->alt_edge_targets + E);
 	if (holder->csum[N] != E)
 		return fail(V2M_ERR_ARGUMENT, "graph_upload: alt_edge_count_csum does not match edge_count");
 

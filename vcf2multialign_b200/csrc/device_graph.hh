@@ -76,11 +76,14 @@ int launch_emit_unaligned(device_graph const &g, u64 const *d_taken, int const *
 	u64 const *d_offsets, void *d_out, cudaStream_t stream);
 
 
-// What a v2m_graph_t points to: the device arrays plus the host copy of alt_edge_count_csum (node id → first edge index).
+// What a v2m_graph_t points to: the device arrays plus host copies of the small node / edge arrays the host-side halves
+// need (alt_edge_count_csum: node id → first edge index; aligned_positions and alt_edge_targets: candidate cut positions).
 struct graph_holder
 {
 	device_graph		g;
 	std::vector<u64>	csum;
+	std::vector<u64>	alnpos;
+	std::vector<u64>	targets;
 
 	~graph_holder()
 	{

@@ -133,6 +133,25 @@ class DeviceGraph:
             return None
         return assigned[: n_seg * founder_count].reshape(founder_count, n_seg).T.copy()
 
+    def find_cut_positions(self, min_distance: int = 0):
+        """find_initial_cut_positions_lambda_min (find_cut_positions.cc:93-211): K4 on the device, recurrence + trace-back on
+        the host inside the library. Returns (cut position node ids, score), or (None, CUT_POSITION_SCORE_MAX) on failure."""
+        cuts = np.zeros(max(int(self.graph.reference_positions.size), 1), np.uint64)
+        n = C.c_uint64(0)
+        score = C.c_uint32(0)
+        found = C.c_int(0)
+        check(lib().v2m_cuda_find_cut_positions(self._h, int(min_distance), ptr(cuts), cuts.size, C.byref(n), C.byref(score), C.byref(found)))
+        if not found.value:
+            return None, int(score.value)
+        return cuts[: n.value].copy(), int(score.value)
+
+    def last_cut_positions_timing(self):
+        ms = (C.c_float * 4)()
+        counts = (C.c_uint64 * 6)()
+        check(lib().v2m_cuda_last_cut_positions_timing(ms, counts))
+        return dict(local_ms=ms[0], compose_ms=ms[1], lists_ms=ms[2], total_host_ms=ms[3], chunks=counts[0], candidates=counts[1],
+                    edges=counts[2], list_pairs=counts[3], cap=counts[4], attempts=counts[5])
+
     def segment_classes(self, cut_positions, want_rhs_eq: bool = True):
         """K3: per-cut class data for find_matchings. Returns a list (one entry per cut ≥ 1) of dicts with
         distinct, first_class, first_is_ref, rhs_eq (or None) and joined (k × 3: lhs_rep, rhs_rep, size; permutation order)."""

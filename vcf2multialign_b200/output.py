@@ -149,8 +149,8 @@ class haplotype_output(output):
 
 
 class founder_sequence_greedy_output(output):
-    """output.hh:81-130. find_cut_positions (find_cut_positions.cc:93-211) is SURVEY §8 row f1 ("next"): until it lands, cut
-    positions are supplied the way --input-cut-positions supplies them (load_cut_positions / set_cut_positions)."""
+    """output.hh:81-130. Cut positions come from find_cut_positions (K4 + host recurrence, find_cut_positions.cc:93-211) or are
+    supplied the way --input-cut-positions supplies them (set_cut_positions ~ load_cut_positions)."""
 
     def __init__(self, chromosome_id, should_output_reference: bool, should_keep_ref_edges: bool, should_output_unaligned: bool,
                  delegate: output_delegate | None = None):
@@ -158,6 +158,8 @@ class founder_sequence_greedy_output(output):
         self.m_should_keep_ref_edges = bool(should_keep_ref_edges)
         self.m_cut_positions = np.zeros(0, np.uint64)
         self.m_assigned_samples = None                    # segments × founders (logical indexing)
+        self.m_min_distance = 0
+        self.m_score = 0
 
     def cut_positions(self):
         return self.m_cut_positions
@@ -167,6 +169,20 @@ class founder_sequence_greedy_output(output):
 
     def assigned_samples(self):
         return self.m_assigned_samples
+
+    def max_segmentation_height(self):
+        return self.m_score
+
+    def find_cut_positions(self, graph, minimum_distance: int, ref_seq=None) -> bool:
+        """output.hh:123, founder_sequence_greedy_output.cc:139-152. `graph`: DeviceGraph, or VariantGraph + ref_seq."""
+        dgraph = graph if isinstance(graph, DeviceGraph) else DeviceGraph(graph, ref_seq)
+        cuts, score = dgraph.find_cut_positions(minimum_distance)
+        if cuts is None:
+            return False
+        self.m_cut_positions = cuts
+        self.m_min_distance = int(minimum_distance)
+        self.m_score = score
+        return True
 
     def find_matchings(self, graph, founder_count: int, ref_seq=None) -> bool:
         """founder_sequence_greedy_output.cc:154-512. `graph`: DeviceGraph, or VariantGraph + ref_seq."""
