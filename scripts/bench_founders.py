@@ -1,13 +1,14 @@
 #!/usr/bin/env python3
-"""Config 3 timing (chr22-shaped synthetic, --founder-sequences=25 --minimum-distance=50): K3 passes, find_matchings, founder rows.
+"""Config 3 timing (chr22-shaped synthetic, --founder-sequences=25 --minimum-distance=50): cut positions (K4 + host
+recurrence), K3 passes, find_matchings, founder rows.
 
-    python scripts/bench_founders.py [--workload c2] [--founders 25] [--min-distance 50] [--cpu-edges 3000]
+    python scripts/bench_founders.py [--workload c2] [--founders 25] [--min-distance 50] [--cpu-edges 3000] [--greedy-cuts]
 
-Cut positions: find_initial_cut_positions_lambda_min is SURVEY §8 row f1 ("next") and its CPU form needs E·H std::map
-operations (≈ 5.5e9 on this shape), so the bench supplies cut positions the way --input-cut-positions would: every node
-that no ALT edge spans is a candidate (find_cut_positions.cc:126-129), taken greedily at >= min-distance aligned columns
-with at least one new ALT edge per segment. The CPU baseline is the oracle's find_matchings sweep on a prefix of the same
-graph (first --cpu-edges ALT edges), scaled per edge column.
+Cut positions come from v2m_cuda_find_cut_positions (find_initial_cut_positions_lambda_min on the device); --greedy-cuts
+instead supplies cut positions the way --input-cut-positions would (every node no ALT edge spans, taken greedily at
+>= min-distance aligned columns). The CPU baseline is the oracle's find_cut_positions + find_matchings on a prefix of the
+same graph (first --cpu-edges ALT edges, a self-contained graph because it ends at a cut), scaled per edge column; the
+device path is run on that same prefix graph and must give identical cut positions, score and assignments.
 """
 from __future__ import annotations
 
@@ -57,6 +58,7 @@ def main():
     ap.add_argument("--min-distance", type=int, default=50)
     ap.add_argument("--cpu-edges", type=int, default=3000)
     ap.add_argument("--iters", type=int, default=3)
+    ap.add_argument("--greedy-cuts", action="store_true")
     args = ap.parse_args()
 
     import vcf2multialign_b200 as v2m
@@ -71,10 +73,27 @@ def main():
     d_paths = L.v2m_cuda_device_alloc(path_bytes)
     synth.path_bits_device(w, d_paths)
     dg = v2m.DeviceGraph(g, w.ref, d_paths_by_edge_and_chrom_copy=d_paths)
-    cuts = greedy_cuts(g, args.min_distance)
+    out = {}
+    if args.greedy_cuts:
+        cuts = greedy_cuts(g, args.min_distance)
+    else:
+        bestc = None
+        for _ in range(args.iters):
+            t0 = time.perf_counter()
+            cuts, score = dg.find_cut_positions(args.min_distance)
+            dt = time.perf_counter() - t0
+            t = dg.last_cut_positions_timing()
+            rec = {"find_cut_positions_s": dt, "k4_local_ms": t["local_ms"], "k4_compose_ms": t["compose_ms"], "k4_lists_ms": t["lists_ms"],
+                   "k4_library_ms": t["total_host_ms"], "k4_chunks": int(t["chunks"]), "k4_candidates": int(t["candidates"]), "k4_list_pairs_read": int(t["list_pairs"]),
+                   "k4_list_cap": int(t["cap"]), "k4_attempts": int(t["attempts"]), "score": int(score)}
+            if bestc is None or dt < bestc["find_cut_positions_s"]:
+                bestc = rec
+        assert cuts is not None
+        out.update(bestc)
+        out["k4_device_ms"] = bestc["k4_local_ms"] + bestc["k4_compose_ms"] + bestc["k4_lists_ms"]
     n_seg = cuts.size - 1
 
-    out = {"workload": f"{args.workload}: {E} ALT edges x {H} chromosome copies, {cuts.size} cut positions (min distance {args.min_distance}), {args.founders} founders"}
+    out["workload"] = f"{args.workload}: {E} ALT edges x {H} chromosome copies, {cuts.size} cut positions (min distance {args.min_distance}), {args.founders} founders"
     # K3 + greedy
     best = None
     for _ in range(args.iters):
@@ -133,16 +152,34 @@ def main():
             label_chars=g.label_chars[: int(g.label_offsets[e_cpu])], paths_ec=sub, paths_ce=None, h_pad=g.h_pad, e_pad=e_pad,
             ploidy_csum=g.ploidy_csum, sample_names=g.sample_names, ref=w.ref[: int(g.reference_positions[last_node]) + 1]))
         f = orc.FounderOutput(og)
-        f.set_cut_positions(cuts[: n_cut_cpu + 1])
+        t0 = time.perf_counter()
+        if args.greedy_cuts:
+            f.set_cut_positions(cuts[: n_cut_cpu + 1])
+        else:
+            assert f.find_cut_positions(args.min_distance)
+        t_cut = time.perf_counter() - t0
         t0 = time.perf_counter()
         ok = f.find_matchings(args.founders)
         t_cpu = time.perf_counter() - t0
-        out["cpu_oracle"] = {"edges": e_cpu, "cuts": n_cut_cpu + 1, "seconds": t_cpu, "us_per_edge_column": 1e6 * t_cpu / e_cpu,
-                             "extrapolated_full_s": t_cpu / e_cpu * E, "ok": bool(ok)}
-        # parity on the prefix: same assignments for the segments both saw (the oracle graph ends at last_node)
-        sub_assigned = f.assigned_samples()
-        assert np.array_equal(sub_assigned[: n_cut_cpu - 1], assigned[: n_cut_cpu - 1]), "GPU and oracle assignments differ on the prefix"
-        out["cpu_oracle"]["prefix_segments_identical"] = int(n_cut_cpu - 1)
+        out["cpu_oracle"] = {"edges": e_cpu, "cuts": int(f.cut_positions().size), "find_cut_positions_s": t_cut, "find_matchings_s": t_cpu,
+                             "us_per_edge_column_cut_positions": 1e6 * t_cut / e_cpu, "us_per_edge_column_matchings": 1e6 * t_cpu / e_cpu,
+                             "extrapolated_full_find_cut_positions_s": t_cut / e_cpu * E, "extrapolated_full_find_matchings_s": t_cpu / e_cpu * E, "ok": bool(ok)}
+        # parity on the prefix graph: the device path on the same graph gives the same cut positions, score and assignments
+        pg = v2m.VariantGraph.from_arrays(dict(
+            reference_positions=g.reference_positions[:N2], aligned_positions=g.aligned_positions[:N2], alt_edge_targets=g.alt_edge_targets[:e_cpu],
+            alt_edge_count_csum=np.concatenate([g.alt_edge_count_csum[:N2], [e_cpu]]).astype(np.uint64), label_offsets=g.label_offsets[: e_cpu + 1],
+            label_chars=g.label_chars[: int(g.label_offsets[e_cpu])], paths_ec=sub, paths_ce=None, h_pad=g.h_pad, e_pad=e_pad,
+            ploidy_csum=g.ploidy_csum, sample_names=g.sample_names))
+        pdg = v2m.DeviceGraph(pg, w.ref[: int(g.reference_positions[last_node]) + 1])
+        if args.greedy_cuts:
+            pcuts = cuts[: n_cut_cpu + 1]
+        else:
+            pcuts, pscore = pdg.find_cut_positions(args.min_distance)
+            assert pcuts.tolist() == f.cut_positions().tolist() and pscore == f.score(), "GPU and oracle cut positions differ on the prefix graph"
+            out["cpu_oracle"]["prefix_cut_positions_identical"] = int(pcuts.size)
+        pm = pdg.find_matchings(pcuts, args.founders)
+        assert np.array_equal(pm, f.assigned_samples()), "GPU and oracle assignments differ on the prefix graph"
+        out["cpu_oracle"]["prefix_segments_identical"] = int(pm.shape[0])
     print(json.dumps(out))
 
 

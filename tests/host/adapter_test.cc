@@ -180,7 +180,9 @@ int main(int argc, char **argv)
 			{
 				log_delegate del;
 				b200::founder_sequence_greedy_output out(nullptr, nullptr, true, false, false, del);
-				out.set_cut_positions(oout.m_cut_positions);
+				expect(out.find_cut_positions(ref_seq, graph, 0), "founder_sequence_greedy_output::find_cut_positions returns true");
+				expect(out.cut_positions() == oout.m_cut_positions, "  cut_positions identical");
+				expect(out.max_segmentation_height() == oout.m_score, "  max_segmentation_height identical");
 				expect(out.find_matchings(ref_seq, graph, founders), "founder_sequence_greedy_output::find_matchings returns true");
 				expect(out.assigned_samples().data == oout.m_assigned_samples.data && out.assigned_samples().rows == oout.m_assigned_samples.rows, "  assigned_samples identical");
 				odel.log.str("");

@@ -458,6 +458,7 @@ public:
 	typedef variant_graph::ploidy_type ploidy_type;
 	constexpr static ploidy_type PLOIDY_MAX{variant_graph::PLOIDY_MAX};
 	typedef std::vector<std::uint64_t> cut_position_vector;
+	typedef ploidy_type cut_position_score_type;																	// find_cut_positions.hh:16
 
 	// lb::matrix<ploidy_type> (column-major, lib/libbio/include/libbio/matrix/matrix.hh:63-68): rows = segments, columns = founders.
 	struct ploidy_matrix
@@ -473,6 +474,8 @@ private:
 	using typename base::row_desc;
 	cut_position_vector	m_cut_positions;
 	ploidy_matrix		m_assigned_samples;
+	std::uint64_t		m_min_distance{};
+	cut_position_score_type	m_score{};
 	bool				m_should_keep_ref_edges{};
 
 	device_plan make_plan(device_graph const &dg, t_graph const &, std::vector<row_desc> &rows) override
@@ -516,9 +519,31 @@ public:
 
 	[[nodiscard]] cut_position_vector const &cut_positions() const { return m_cut_positions; }
 	[[nodiscard]] ploidy_matrix const &assigned_samples() const { return m_assigned_samples; }
-	// find_cut_positions (find_cut_positions.cc:93-211) is SURVEY §8 row f1; until it lands cut positions come in the way
-	// --input-cut-positions supplies them (load_cut_positions in the reference).
+	[[nodiscard]] cut_position_score_type max_segmentation_height() const { return m_score; }								// output.hh:124
+	// What load_cut_positions (--input-cut-positions) provides in the reference.
 	void set_cut_positions(cut_position_vector cuts) { m_cut_positions = std::move(cuts); }
+
+	// output.hh:123, founder_sequence_greedy_output.cc:139-152 → find_initial_cut_positions_lambda_min (find_cut_positions.cc:93-211).
+	[[nodiscard]] bool find_cut_positions(sequence_type const &ref_seq, t_graph const &graph, std::uint64_t const minimum_distance)
+	{
+		device_graph const dg(ref_seq, graph);
+		return find_cut_positions(dg, graph, minimum_distance);
+	}
+
+	[[nodiscard]] bool find_cut_positions(device_graph const &dg, t_graph const &graph, std::uint64_t const minimum_distance)
+	{
+		std::vector<std::uint64_t> cuts(std::max<std::size_t>(graph.reference_positions.size(), 1));
+		std::uint64_t n(0);
+		std::uint32_t score(0);
+		int found(0);
+		check(v2m_cuda_find_cut_positions(dg.get(), minimum_distance, cuts.data(), cuts.size(), &n, &score, &found));
+		if (!found) return false;
+		cuts.resize(n);
+		m_cut_positions.assign(cuts.begin(), cuts.end());
+		m_min_distance = minimum_distance;
+		m_score = score;
+		return true;
+	}
 
 	[[nodiscard]] bool find_matchings(sequence_type const &ref_seq, t_graph const &graph, ploidy_type const founder_count)
 	{
