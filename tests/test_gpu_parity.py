@@ -63,6 +63,16 @@ def test_transpose_tile_edges(v2m, rows, cols):
     assert np.array_equal(got, orc.transpose(src, rows, cols))
 
 
+@pytest.mark.parametrize("rows,cols", [(64, 64), (64, 192), (128, 320), (192, 128), (256, 1088), (320, 64), (512, 448), (1024, 192), (2048, 704),
+                                       (5056, 2112), (5056, 64), (8192, 384), (14080, 192)])
+def test_transpose_more_shapes(v2m, rows, cols):
+    """Ragged last tiles in both directions, the 5,008-haplotype line length, the 8,192-copy limit and beyond."""
+    rng = np.random.default_rng(rows * 13 + cols)
+    src = rng.integers(0, 2**64 - 1, rows * cols // 64, dtype=np.uint64)
+    got = v2m.transpose_matrix(src, rows, cols)
+    assert np.array_equal(got, orc.transpose(src, rows, cols))
+
+
 def test_transpose_large_involution(v2m):
     """Bigger than the oracle finishes quickly: T(T(x)) == x plus population count and a sampled bit check."""
     rows, cols = 5056, 64 * 3000

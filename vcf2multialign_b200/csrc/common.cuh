@@ -101,12 +101,32 @@ template <int t_pending>
 __device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read %0;" :: "n"(t_pending) : "memory"); }
 
 // In-register 32×32 bit-matrix transpose, LSB-first on both sides: on return bit i of a[j] is what bit j of a[i] was.
-// Five block-swap stages (16, 8, 4, 2, 1); with full unrolling a[] lives in registers.
+// Five block-swap stages (16, 8, 4, 2, 1); with full unrolling a[] lives in registers. On the device the 16- and 8-bit
+// stages move whole bytes, so each pair costs two PRMT instead of five shift / logic operations.
 __host__ __device__ __forceinline__ void transpose32(u32 (&a)[32])
 {
-	u32 m(0x0000ffffu);
+#ifdef __CUDA_ARCH__
 #pragma unroll
+	for (int k = 0; k < 16; ++k)
+	{
+		u32 const x(a[k]), y(a[k + 16]);
+		a[k] = __byte_perm(x, y, 0x5410);
+		a[k + 16] = __byte_perm(x, y, 0x7632);
+	}
+#pragma unroll
+	for (int k = 0; k < 32; k = (k + 8 + 1) & ~8)
+	{
+		u32 const x(a[k]), y(a[k + 8]);
+		a[k] = __byte_perm(x, y, 0x6240);
+		a[k + 8] = __byte_perm(x, y, 0x7351);
+	}
+	u32 m(0x0f0f0f0fu);
+#pragma unroll
+	for (int j = 4; j != 0; j >>= 1, m ^= (m << j))
+#else
+	u32 m(0x0000ffffu);
 	for (int j = 16; j != 0; j >>= 1, m ^= (m << j))
+#endif
 	{
 #pragma unroll
 		for (int k = 0; k < 32; k = (k + j + 1) & ~j)

@@ -13,8 +13,13 @@
 //           (common.cuh:transpose32) — ~12 instructions per 128 B per warp, an order of magnitude fewer than 32
 //           ballots per sub-tile, which would leave the kernel issue-bound instead of HBM-bound;
 //   store   lanes are laid out 16 line groups × 2 word columns, so each STG.32 of a warp writes two full 64-byte
-//           runs of two destination lines; consecutive CTAs (blockIdx.x) extend the same destination lines, so the
-//           126 MB L2 merges them into full lines before write-back.
+//           runs of two destination lines; CTAs of consecutive line tiles (blockIdx.y) extend the same destination lines, so
+//           the 126 MB L2 merges them into full lines before write-back.
+//   grid    row bands vary fastest. A 128-byte piece of a source line starts at an 8-byte boundary only, so it shares its
+//           first and last sectors with the pieces of the neighbouring bands; with the bands of one line tile resident
+//           together those sectors leave DRAM once (ncu, c5: DRAM reads 3.81 GB for 3.79 GB algorithmic; with line tiles
+//           fastest it was 7.41 GB). A variant that read whole lines through one bulk copy per CTA and stored 16-byte runs
+//           was measured and dropped: half-sector stores cost read-modify-write traffic in the L2 (5.0 GB written, 4.1 ms).
 //
 // Algorithmic bytes: 2 · R · C / 8 (each bit read once, written once). Roofline: HBM read + write.
 #include "common.cuh"
@@ -31,8 +36,10 @@ transpose_bits_kernel(u64 const * __restrict__ src, u32 * __restrict__ dst, u64 
 	// R64 = source rows / 64 = 64-bit words per source line; C = number of source lines.
 	extern __shared__ __align__(16) u64 tile[];					// K1_TC * K1_TW / 2 words = 64 KiB (dynamic: above the 48 KiB static limit)
 
-	u64 const c0(u64(blockIdx.x) * K1_TC);
-	u64 const p0(u64(blockIdx.y) * (K1_TW / 2));				// first 64-bit word (pair) of the row band
+	// Row bands vary fastest (blockIdx.x): the CTAs that share the boundary sectors of a 128-byte piece of a source line run
+	// together, so those sectors come out of DRAM once and out of the L2 afterwards.
+	u64 const c0(u64(blockIdx.y) * K1_TC);
+	u64 const p0(u64(blockIdx.x) * (K1_TW / 2));				// first 64-bit word (pair) of the row band
 	unsigned const tid(threadIdx.x);
 
 	// ---- load -------------------------------------------------------------------------------------------
@@ -85,11 +92,13 @@ transpose_bits_kernel(u64 const * __restrict__ src, u32 * __restrict__ dst, u64 
 }
 
 
+
 int launch_transpose_bits(void const *d_src, u64 rows, u64 cols, void *d_dst, cudaStream_t stream)
 {
 	if (0 == cols || 0 == rows) return 0;
 	u64 const R64(rows / 64);
-	dim3 const grid(unsigned((cols + K1_TC - 1) / K1_TC), unsigned((R64 + K1_TW / 2 - 1) / (K1_TW / 2)));
+	dim3 const grid(unsigned((R64 + K1_TW / 2 - 1) / (K1_TW / 2)), unsigned((cols + K1_TC - 1) / K1_TC));
+	if (grid.y > 65535u) return fail(1, "transpose_bits: more than 33,553,920 source lines in one launch");
 	constexpr int smem_bytes(K1_TC * (K1_TW / 2) * sizeof(u64));
 	V2M_CUDA_TRY(cudaFuncSetAttribute(transpose_bits_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));	// per device
 	transpose_bits_kernel<<<grid, K1_THREADS, smem_bytes, stream>>>(static_cast<u64 const *>(d_src), static_cast<u32 *>(d_dst), R64, cols);
