@@ -129,6 +129,9 @@ int v2m_cuda_emit_rows_device(v2m_plan_t p, uint32_t row_begin, uint32_t row_end
 /* Host variant: kernels fill device tiles that are copied into `out` (any host memory; pinned is faster). */
 int v2m_cuda_emit_rows(v2m_plan_t p, uint32_t row_begin, uint32_t row_end, uint64_t col_begin, uint64_t col_end,
                        uint8_t *out, uint64_t pitch);
+/* The host variants keep two device staging tiles and two streams per calling host thread between calls; this frees them
+ * (they are also freed when the thread ends). */
+void v2m_cuda_release_staging(void);
 /* Unaligned rows (--unaligned: no gap fill): row r is written at out + offsets[r - row_begin], length from
  * v2m_cuda_plan_row_lengths(…, 1, …). */
 int v2m_cuda_emit_rows_unaligned(v2m_plan_t p, uint32_t row_begin, uint32_t row_end, const uint64_t *offsets, uint8_t *out);

@@ -429,6 +429,54 @@ int v2m_cuda_emit_rows_device(v2m_plan_t p, uint32_t row_begin, uint32_t row_end
 	return launch_emit_rows(*p->p.graph, p->p.taken, row_begin, row_end, col_begin, col_end, d_out, pitch, static_cast<cudaStream_t>(stream));
 }
 
+namespace {
+	// Two device tiles + two streams of the calling host thread, grown on demand, released with v2m_cuda_release_staging()
+	// or when the thread ends.
+	struct staging_area
+	{
+		u8				*d_buf[2] = {nullptr, nullptr};
+		cudaStream_t	streams[2] = {nullptr, nullptr};
+		u64				capacity{};
+		int				device{-1};
+
+		void release()
+		{
+			for (int i(0); i < 2; ++i)
+			{
+				if (d_buf[i]) cudaFree(d_buf[i]);
+				if (streams[i]) cudaStreamDestroy(streams[i]);
+				d_buf[i] = nullptr; streams[i] = nullptr;
+			}
+			capacity = 0; device = -1;
+		}
+
+		int reserve(u64 const bytes)
+		{
+			int dev(0);
+			V2M_CUDA_TRY(cudaGetDevice(&dev));
+			if (dev != device) { release(); device = dev; }
+			for (int i(0); i < 2; ++i)
+				if (!streams[i] && cudaSuccess != cudaStreamCreateWithFlags(&streams[i], cudaStreamNonBlocking))
+					return fail(V2M_ERR_CUDA, "cudaStreamCreate failed");
+			if (bytes <= capacity) return V2M_OK;
+			for (int i(0); i < 2; ++i)
+			{
+				if (d_buf[i]) { cudaFree(d_buf[i]); d_buf[i] = nullptr; }
+				capacity = 0;
+				if (int const st = dev_alloc(d_buf[i], bytes)) return st;
+			}
+			capacity = bytes;
+			return V2M_OK;
+		}
+
+		~staging_area() { release(); }
+	};
+
+	staging_area &thread_staging() { thread_local staging_area sa; return sa; }
+}
+
+void v2m_cuda_release_staging(void) { thread_staging().release(); }
+
 int v2m_cuda_emit_rows(v2m_plan_t p, uint32_t row_begin, uint32_t row_end, uint64_t col_begin, uint64_t col_end,
 	uint8_t *out, uint64_t pitch)
 {
@@ -444,34 +492,22 @@ int v2m_cuda_emit_rows(v2m_plan_t p, uint32_t row_begin, uint32_t row_end, uint6
 	u64 const budget(u64(256) << 20);	// bytes per staging buffer
 	u32 const chunk_rows(u32(std::max<u64>(1, std::min<u64>(row_end - row_begin, budget / d_pitch))));
 
-	u8 *d_buf[2] = {nullptr, nullptr};
-	cudaStream_t streams[2] = {nullptr, nullptr};
-	int st(V2M_OK);
-	do
+	// Staging tiles and streams are kept per host thread: a caller streaming a plan block by block (bench.py's end-to-end leg,
+	// the C++ adapters) should not pay two cudaMalloc / cudaFree pairs — device-wide synchronisations — per call.
+	staging_area &sa(thread_staging());
+	int st(sa.reserve(u64(chunk_rows) * d_pitch));
+	if (st) return st;
+	int k(0);
+	for (u32 r0(row_begin); r0 < row_end && !st; r0 += chunk_rows, k ^= 1)
 	{
-		for (int i(0); i < 2 && !st; ++i)
-		{
-			if ((st = dev_alloc(d_buf[i], u64(chunk_rows) * d_pitch))) break;
-			if (cudaSuccess != cudaStreamCreateWithFlags(&streams[i], cudaStreamNonBlocking)) st = fail(V2M_ERR_CUDA, "cudaStreamCreate failed");
-		}
-		if (st) break;
-		int k(0);
-		for (u32 r0(row_begin); r0 < row_end && !st; r0 += chunk_rows, k ^= 1)
-		{
-			u32 const r1(std::min<u64>(row_end, u64(r0) + chunk_rows));
-			// Work on a stream is ordered, so buffer k is free again once its previous copy has been issued on the same stream.
-			if ((st = launch_emit_rows(*p->p.graph, p->p.taken, r0, r1, cb, col_end, d_buf[k], d_pitch, streams[k]))) break;
-			if (cudaSuccess != cudaMemcpy2DAsync(out + u64(r0 - row_begin) * pitch, pitch, d_buf[k] + skip, d_pitch, width, r1 - r0, cudaMemcpyDeviceToHost, streams[k]))
-				st = fail(V2M_ERR_CUDA, "D2H copy of rows failed");
-		}
-		for (int i(0); i < 2; ++i)
-			if (streams[i] && cudaSuccess != cudaStreamSynchronize(streams[i]) && !st) st = fail(V2M_ERR_CUDA, std::string("emit_rows: ") + cudaGetErrorString(cudaGetLastError()));
-	} while (false);
-	for (int i(0); i < 2; ++i)
-	{
-		if (streams[i]) cudaStreamDestroy(streams[i]);
-		cudaFree(d_buf[i]);
+		u32 const r1(std::min<u64>(row_end, u64(r0) + chunk_rows));
+		// Work on a stream is ordered, so buffer k is free again once its previous copy has been issued on the same stream.
+		if ((st = launch_emit_rows(*p->p.graph, p->p.taken, r0, r1, cb, col_end, sa.d_buf[k], d_pitch, sa.streams[k]))) break;
+		if (cudaSuccess != cudaMemcpy2DAsync(out + u64(r0 - row_begin) * pitch, pitch, sa.d_buf[k] + skip, d_pitch, width, r1 - r0, cudaMemcpyDeviceToHost, sa.streams[k]))
+			st = fail(V2M_ERR_CUDA, "D2H copy of rows failed");
 	}
+	for (int i(0); i < 2; ++i)
+		if (cudaSuccess != cudaStreamSynchronize(sa.streams[i]) && !st) st = fail(V2M_ERR_CUDA, std::string("emit_rows: ") + cudaGetErrorString(cudaGetLastError()));
 	return st;
 }
 
