@@ -1,10 +1,11 @@
 // Host half of founder_sequence_greedy_output::find_matchings (libvcf2multialign/founder_sequence_greedy_output.cc:154-512):
 // the per-cut class data comes from K3 (founders.cu) and the greedy assignment of founders to class representatives runs
-// here, on the host, with the same libstdc++ containers and std::sort the reference uses — the assignment is a short
-// sequential pass per cut whose tie behaviour depends on std::sort's introsort and on std::multimap's insertion order
-// (SURVEY.md §7 "hard parts"), so it is kept as host C++ by design.
+// here, on the host, with the same std::sort the reference uses — the assignment is a short sequential pass per cut whose tie
+// behaviour depends on std::sort's introsort and on std::multimap's ordering of equal keys (SURVEY.md §7 "hard parts"), so
+// it is kept as host C++ by design. The reference's std::multimap<class, founder> holds at most founder_count entries and is
+// rebuilt at every cut (27 M node allocations on c3); it is replaced by a sorted vector with the same observable behaviour.
 #include <algorithm>
-#include <map>
+#include <utility>
 #include <vector>
 
 #include "../../include/v2m_cuda.h"
@@ -26,21 +27,59 @@ namespace {
 		bool operator<(joined_class const &other) const { return size < other.size; }
 	};
 
+	// std::multimap<u32, u32> as the reference uses it (founder_…cc:174, 283, 340-360, 441-447), on a sorted vector:
+	// insert places the pair after the pairs with an equal key (libstdc++ _M_get_insert_equal_pos descends to the right on
+	// equality), find returns the first pair with the key (lower bound), begin is the first pair of the smallest key.
+	class flat_multimap
+	{
+		std::vector<std::pair<u32, u32>>	m_items;
+	public:
+		typedef std::vector<std::pair<u32, u32>>::iterator iterator;
+		iterator begin() { return m_items.begin(); }
+		iterator end() { return m_items.end(); }
+		bool empty() const { return m_items.empty(); }
+		void clear() { m_items.clear(); }
+		void erase(iterator it) { m_items.erase(it); }
+		void emplace(u32 const key, u32 const value)
+		{
+			auto const it(std::upper_bound(m_items.begin(), m_items.end(), key, [](u32 const k, std::pair<u32, u32> const &p) { return k < p.first; }));
+			m_items.insert(it, {key, value});
+		}
+		iterator find(u32 const key)
+		{
+			auto const it(std::lower_bound(m_items.begin(), m_items.end(), key, [](std::pair<u32, u32> const &p, u32 const k) { return p.first < k; }));
+			return (it != m_items.end() && it->first == key) ? it : m_items.end();
+		}
+	};
+
+	// The reference's "reserved" bit vector (founder_…cc:175, 333), cleared per cut: a stamp per chromosome copy instead of an
+	// O(H) fill per cut.
+	class stamp_set
+	{
+		std::vector<u32>	m_stamp;
+		u32					m_epoch{1};
+	public:
+		explicit stamp_set(u32 const n): m_stamp(n, 0) {}
+		void clear() { if (0 == ++m_epoch) { std::fill(m_stamp.begin(), m_stamp.end(), 0); m_epoch = 1; } }
+		bool test(u32 const i) const { return m_stamp[i] == m_epoch; }
+		void set(u32 const i) { m_stamp[i] = m_epoch; }
+	};
+
 	// State carried from cut to cut (founder_sequence_greedy_output.cc:174-176).
 	class founder_matcher
 	{
 		u32							m_founders;
 		u64							m_segments;
 		u32							*m_assigned;			// column-major: (segment, founder) → m_assigned[founder * segments + segment]
-		std::multimap<u32, u32>		m_by_class;				// class representative on the current lhs → founder
-		std::vector<u8>				m_reserved;				// by chromosome copy
+		flat_multimap				m_by_class;				// class representative on the current lhs → founder
+		stamp_set					m_reserved;				// by chromosome copy
 		std::vector<u32>			m_arbitrary_rhs;
 
 		u32 &slot(u64 const segment, u32 const founder) { return m_assigned[u64(founder) * m_segments + segment]; }
 
 	public:
 		founder_matcher(u32 copies, u32 founders, u64 segments, u32 *assigned):
-			m_founders(founders), m_segments(segments), m_assigned(assigned), m_reserved(copies, 0) {}
+			m_founders(founders), m_segments(segments), m_assigned(assigned), m_reserved(copies) {}
 
 		// :268-320 — founders of the first segment, largest joined classes first; every lhs class gets one founder
 		// before any class gets a second one.
@@ -57,14 +96,14 @@ namespace {
 			});
 			for (auto it(by_size.rbegin()); it != by_size.rend(); ++it)
 			{
-				if (m_reserved[it->lhs])
+				if (m_reserved.test(it->lhs))
 				{
 					if (free_founders) { --free_founders; place(*it); }
 				}
 				else if (to_reserve)
 				{
 					--to_reserve;
-					m_reserved[it->lhs] = 1;
+					m_reserved.set(it->lhs);
 					place(*it);
 				}
 			}
@@ -83,7 +122,7 @@ namespace {
 		// :331-447 — carry the founders across the cut that ends segment `segment - 1` (cut index `segment`).
 		int extend(u64 const segment, std::vector<joined_class> const &by_size, u32 const rhs_distinct)
 		{
-			std::fill(m_reserved.begin(), m_reserved.end(), 0);
+			m_reserved.clear();
 			m_arbitrary_rhs.clear();
 			u32 free_founders(m_founders);
 			u32 to_reserve(std::min(free_founders, rhs_distinct));
@@ -113,7 +152,7 @@ namespace {
 				bool progressed(false);
 				for (auto it(by_size.rbegin()); it != by_size.rend(); ++it)
 				{
-					if (m_reserved[it->rhs])
+					if (m_reserved.test(it->rhs))
 					{
 						if (free_founders)
 						{
@@ -124,7 +163,7 @@ namespace {
 					else if (to_reserve)
 					{
 						--to_reserve;
-						if (follow(*it)) m_reserved[it->rhs] = 1;
+						if (follow(*it)) m_reserved.set(it->rhs);
 						else m_arbitrary_rhs.push_back(it->rhs);
 					}
 				}
@@ -135,11 +174,11 @@ namespace {
 
 			// Step 4 (:417-426).
 			for (u32 const rhs : m_arbitrary_rhs)
-				if (!m_reserved[rhs])
+				if (!m_reserved.test(rhs))
 				{
 					if (!take_any(rhs))
 						return fail(V2M_ERR_STATE, "find_matchings: no founder left to connect arbitrarily (the reference asserts, founder_sequence_greedy_output.cc:355)");
-					m_reserved[rhs] = 1;
+					m_reserved.set(rhs);
 				}
 
 			// Step 5 (:429-438).
@@ -152,7 +191,7 @@ namespace {
 			// :441-447
 			m_by_class.clear();
 			for (u32 f(0); f < m_founders; ++f)
-				m_by_class.insert({slot(segment, f), f});
+				m_by_class.emplace(slot(segment, f), f);
 			return V2M_OK;
 		}
 	};
@@ -177,17 +216,16 @@ extern "C" int v2m_cuda_find_matchings(v2m_graph_t g, const uint64_t *cut_positi
 	std::vector<u64> offsets;
 	if (int const st = segment_classes_host(*g, cut_positions, n_cuts, false, 0, rhs_eq, distinct, first_class, first_is_ref, offsets, joined)) return st;
 
+	std::vector<joined_class> by_size;
 	auto const classes_of_cut([&](u64 const c) {		// cut index c >= 1 → its joined classes, in permutation order
-		std::vector<joined_class> out;
-		out.reserve(offsets[c] - offsets[c - 1]);
-		for (u64 i(offsets[c - 1]); i < offsets[c]; ++i) out.push_back({joined[3 * i], joined[3 * i + 1], joined[3 * i + 2]});
-		return out;
+		by_size.clear();
+		for (u64 i(offsets[c - 1]); i < offsets[c]; ++i) by_size.push_back({joined[3 * i], joined[3 * i + 1], joined[3 * i + 2]});
 	});
 
 	if (2 == n_cuts)
 	{
 		// The trivial case (:474-509): one segment, founders take the largest classes.
-		auto by_size(classes_of_cut(1));
+		classes_of_cut(1);
 		std::sort(by_size.begin(), by_size.end());
 		// rhs_first_path_is_ref was reset to true when the only cut was handled (:456-457) and no edge follows the sink,
 		// so the test at :500 reduces to !m_should_keep_ref_edges.
@@ -203,7 +241,7 @@ extern "C" int v2m_cuda_find_matchings(v2m_graph_t g, const uint64_t *cut_positi
 	for (u64 c(2); c < n_cuts; ++c)
 	{
 		// In the reference's loop this is cut_pos_idx = c - 1: lhs = segment c - 2, rhs = segment c - 1.
-		auto by_size(classes_of_cut(c));
+		classes_of_cut(c);
 		std::sort(by_size.begin(), by_size.end());														// :258
 		if (!keep_ref_edges && first_is_ref[c - 2] && first_is_ref[c - 1])								// :261-266
 			std::erase_if(by_size, [&](joined_class const &jc) { return first_class[c - 2] == jc.lhs && first_class[c - 1] == jc.rhs; });
