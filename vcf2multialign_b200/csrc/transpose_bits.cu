@@ -20,6 +20,9 @@
 //           together those sectors leave DRAM once (ncu, c5: DRAM reads 3.81 GB for 3.79 GB algorithmic; with line tiles
 //           fastest it was 7.41 GB). A variant that read whole lines through one bulk copy per CTA and stored 16-byte runs
 //           was measured and dropped: half-sector stores cost read-modify-write traffic in the L2 (5.0 GB written, 4.1 ms).
+//           Also measured and dropped on c5: one persistent CTA per SM with two cp.async-filled tile buffers (2.08 ms: 16
+//           warps per SM do not cover the transpose's issue time) and 256-line tiles with 4 CTAs per SM (1.96 ms: 32-byte
+//           store runs); this kernel runs 1.61 ms there.
 //
 // Algorithmic bytes: 2 · R · C / 8 (each bit read once, written once). Roofline: HBM read + write.
 #include "common.cuh"
