@@ -353,11 +353,26 @@ inline vcf_file read_vcf(char const *path)
 // ---------------------------------------------------------------------------------------
 struct overlap_report { u64 lineno; u64 ref_pos; std::string var_id; std::string sample; u32 chrom_copy; u32 gt; };
 
+// What the "Paths" loop of build_variant_graph (variant_graph.cc:379-425) consumes and produces, per handled record, in
+// flat form: the input and expected output of the device's genotype ingestion. Filled only when
+// build_delegate::trace is set.
+struct build_trace
+{
+	u32							copies{};			// ploidy_csum.back()
+	std::vector<std::uint16_t>	gt;					// [records][copies]: sample_gt.alt by output row index (0 = REF, NULL_ALLELE = '.')
+	std::vector<u64>			alt_offsets{0};		// [records + 1] into edges_by_alt
+	std::vector<u64>			edges_by_alt;		// edge index of every ALT, EDGE_MAX where the ALT has no edge
+	std::vector<u64>			ref_pos;			// [records]
+	std::vector<u64>			edge_target_pos;	// [edges] reference position of the edge's target node
+	std::vector<u64>			overlaps;			// (record, row) pairs in the order reported (:405-418)
+};
+
 struct build_delegate
 {
 	std::function<bool(std::string_view, u32)>	should_include = [](std::string_view, u32){ return true; };
 	std::vector<overlap_report>				overlaps;
 	std::vector<u64>							ref_mismatches;	// 1-based variant indices; building stops at the first
+	build_trace									*trace{};
 };
 
 inline void build_variant_graph(
@@ -500,12 +515,24 @@ inline void build_variant_graph(
 		}
 
 		// Paths (:379-425).
+		if (delegate.trace)
+		{
+			build_trace &tr(*delegate.trace);
+			tr.copies = graph.ploidy_csum.back();
+			tr.gt.resize(tr.gt.size() + tr.copies, 0);
+			tr.edges_by_alt.insert(tr.edges_by_alt.end(), edges_by_alt.begin(), edges_by_alt.end());
+			tr.alt_offsets.push_back(tr.edges_by_alt.size());
+			tr.ref_pos.push_back(ref_pos);
+			tr.edge_target_pos.insert(tr.edge_target_pos.end(), current_edge_targets.begin(), current_edge_targets.end());
+		}
 		for (auto const &sc : included)
 		{
 			auto const &gt(var.gt[sc.sample_vcf]);
 			ORACLE_ASSERT(sc.copy_vcf < gt.size());
 			u64 const base_idx(graph.ploidy_csum[sc.sample_out]);
 			auto const alt_idx(gt[sc.copy_vcf]);
+			if (delegate.trace)
+				delegate.trace->gt[delegate.trace->gt.size() - delegate.trace->copies + base_idx + sc.copy_out] = alt_idx;
 			if (0 == alt_idx) continue;
 			if (NULL_ALLELE == alt_idx) continue;
 			ORACLE_ASSERT(u64(alt_idx - 1) < edges_by_alt.size());
@@ -513,7 +540,10 @@ inline void build_variant_graph(
 			if (EDGE_MAX == edge_idx) continue;
 			u64 const row_idx(base_idx + sc.copy_out);
 			if (ref_pos < target_ref_positions_by_chrom_copy[row_idx])
+			{
 				delegate.overlaps.push_back({var.lineno + vf.last_header_lineno, ref_pos, var.id, vf.sample_names[sc.sample_vcf], sc.copy_vcf, alt_idx});
+				if (delegate.trace) { delegate.trace->overlaps.push_back(delegate.trace->ref_pos.size() - 1); delegate.trace->overlaps.push_back(row_idx); }
+			}
 			ORACLE_ASSERT(edge_idx - min_edge < current_edge_targets.size());
 			target_ref_positions_by_chrom_copy[row_idx] = current_edge_targets[edge_idx - min_edge];
 			graph.paths_by_edge_and_chrom_copy.set(row_idx, edge_idx);
