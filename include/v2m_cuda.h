@@ -190,6 +190,30 @@ int v2m_cuda_find_cut_positions(v2m_graph_t g, uint64_t min_distance, uint64_t *
  * list capacity per candidate, list extraction attempts}. */
 int v2m_cuda_last_cut_positions_timing(float *ms4, uint64_t *counts6);
 
+/* --- K5: the "Paths" loop of build_variant_graph (libvcf2multialign/variant_graph.cc:379-425): path bits from parsed GT
+ *         fields (the step before the path) --------------------------------------------------------- */
+#define V2M_GT_NULL 0xffffu   /* vcf::sample_genotype::NULL_ALLELE as passed here ('.' in a GT field) */
+/* gt[r * n_copies + row]: the GT allele (sample_gt.alt) of handled record r for output row `row` = ploidy_csum[sample] + copy
+ * (0 = REF, V2M_GT_NULL = null, a > 0 = ALT a). ALT a of record r has edge edges_by_alt[alt_offsets[r] + a - 1], or EDGE_MAX
+ * (all ones) if it got none (variant_graph.cc:328-364). The result is paths_by_edge_and_chrom_copy (rows = h_pad, cols =
+ * e_pad), zero outside the set bits. A genotype naming an ALT its record does not have gives V2M_ERR_ARGUMENT (the reference
+ * asserts, :399).
+ * Overlap reports (:405-418), optional (n_overlaps != NULL, record_ref_pos and edge_target_pos given): for every chromosome
+ * copy, in record order, (record, row) is reported when record_ref_pos[r] < the target reference position of the copy's
+ * previous ALT edge (edge_target_pos[edge], n_edges entries); pairs come back sorted by record, then row, i.e. in the
+ * reference's reporting order. If overlap_cap is too small: V2M_ERR_ARGUMENT with the needed count in *n_overlaps. */
+int v2m_cuda_paths_from_genotypes(const uint16_t *gt, uint64_t n_records, uint32_t n_copies,
+                                  const uint64_t *alt_offsets /* [n_records + 1] */, const uint64_t *edges_by_alt,
+                                  const uint64_t *record_ref_pos, const uint64_t *edge_target_pos, uint64_t n_edges,
+                                  uint64_t h_pad, uint64_t e_pad, uint64_t *paths_by_edge_and_chrom_copy,
+                                  uint64_t *overlaps /* [overlap_cap][2] */, uint64_t overlap_cap, uint64_t *n_overlaps);
+/* Same, the matrix stays on the device (d_paths: e_pad * h_pad / 8 bytes), ready for v2m_graph_view.paths_on_device. */
+int v2m_cuda_paths_from_genotypes_device(const uint16_t *gt, uint64_t n_records, uint32_t n_copies,
+                                         const uint64_t *alt_offsets, const uint64_t *edges_by_alt,
+                                         const uint64_t *record_ref_pos, const uint64_t *edge_target_pos, uint64_t n_edges,
+                                         uint64_t h_pad, uint64_t e_pad, void *d_paths,
+                                         uint64_t *overlaps, uint64_t overlap_cap, uint64_t *n_overlaps);
+
 /* --- synthetic workloads (measurement infrastructure) ------------------------------------------------ */
 /* Fills d_dst (device, e_pad × h_pad/64 words = paths_by_edge_and_chrom_copy) with LD-structured path bits that are a
  * pure function of (seed, chromosome copy, site); per edge: its site, its 0-based ALT number, the site's ALT count. */
@@ -206,6 +230,9 @@ int v2m_cuda_time_emit_rows(v2m_plan_t p, uint32_t row_begin, uint32_t row_end, 
  * counts4 = {chunks, cut positions, ALT edges, joined triples}. */
 int v2m_cuda_last_segment_classes_timing(float *ms3, uint64_t *counts4);
 int v2m_cuda_time_transpose_bits(const void *d_src, uint64_t rows, uint64_t cols, void *d_dst, int iters, float *ms_mean);
+/* K5 alone on GT values, offsets and edge indices already resident in HBM. */
+int v2m_cuda_time_ingest_genotypes(const void *d_gt, uint64_t n_records, uint32_t n_copies, const void *d_alt_offsets, const void *d_edges_by_alt,
+                                   uint64_t h_pad, uint64_t e_pad, void *d_paths, int iters, float *ms_mean);
 
 #ifdef __cplusplus
 }

@@ -18,6 +18,7 @@ namespace {
 		variant_graph		graph;
 		std::vector<char>	ref_seq;
 		build_delegate		build;
+		build_trace			trace;
 		u64					handled_variants{};
 		u64					chr_id_mismatches{};
 		// flattened labels
@@ -81,10 +82,30 @@ void *orc_graph_from_files(char const *fasta_path, char const *vcf_path, char co
 	if (guarded([&]{
 		read_single_fasta_sequence(fasta_path, box->ref_seq, nullptr);
 		auto const vf(read_vcf(vcf_path));
+		box->build.trace = &box->trace;
 		build_variant_graph(box->ref_seq, vf, chr_id, box->graph, box->build, &box->handled_variants, &box->chr_id_mismatches);
 		box->flatten();
 	})) return nullptr;
 	return box.release();
+}
+
+// The genotype block behind the graph's path bits (build_trace): dims6 = {records, copies, alts, edges, overlap pairs, 0}.
+void orc_graph_trace_dims(void *h, u64 *dims6)
+{
+	auto const &t(static_cast<graph_box *>(h)->trace);
+	dims6[0] = t.ref_pos.size(); dims6[1] = t.copies; dims6[2] = t.edges_by_alt.size();
+	dims6[3] = t.edge_target_pos.size(); dims6[4] = t.overlaps.size() / 2; dims6[5] = 0;
+}
+
+void orc_graph_trace_copy(void *h, std::uint16_t *gt, u64 *alt_offsets, u64 *edges_by_alt, u64 *ref_pos, u64 *edge_target_pos, u64 *overlaps)
+{
+	auto const &t(static_cast<graph_box *>(h)->trace);
+	std::copy(t.gt.begin(), t.gt.end(), gt);
+	std::copy(t.alt_offsets.begin(), t.alt_offsets.end(), alt_offsets);
+	std::copy(t.edges_by_alt.begin(), t.edges_by_alt.end(), edges_by_alt);
+	std::copy(t.ref_pos.begin(), t.ref_pos.end(), ref_pos);
+	std::copy(t.edge_target_pos.begin(), t.edge_target_pos.end(), edge_target_pos);
+	std::copy(t.overlaps.begin(), t.overlaps.end(), overlaps);
 }
 
 // Graph from flat arrays (synthetic workloads). paths_ec = words of paths_by_edge_and_chrom_copy

@@ -47,6 +47,10 @@ def lib():
     L.orc_graph_from_arrays.argtypes = [u64, u64, vp, vp, vp, vp, vp, vp, vp, vp, u64, u64, u32, vp, cp, vp, u64]
     L.orc_graph_free.argtypes = [vp]
     L.orc_graph_dims.argtypes = [vp, vp]
+    L.orc_graph_trace_dims.restype = None
+    L.orc_graph_trace_dims.argtypes = [vp, vp]
+    L.orc_graph_trace_copy.restype = None
+    L.orc_graph_trace_copy.argtypes = [vp] * 7
     L.orc_graph_copy.argtypes = [vp] * 12
     L.orc_graph_overlap.restype = C.c_longlong
     L.orc_graph_overlap.argtypes = [vp, u64, vp, vp, u64]
@@ -209,6 +213,22 @@ class Graph:
         a["label_chars"] = a["label_chars"].tobytes()
         self._arrays = a
         return a
+
+    def genotype_trace(self) -> dict:
+        """What the "Paths" loop of build_variant_graph consumed (variant_graph.cc:379-425), flat: gt[records][copies],
+        alt_offsets, edges_by_alt, ref_pos per record, target reference position per edge, reported overlaps (record, row)."""
+        d = np.zeros(6, np.uint64)
+        lib().orc_graph_trace_dims(self._h, _ptr(d))
+        R, Hc, n_alts, n_edges, n_ov = (int(x) for x in d[:5])
+        t = dict(gt=np.zeros(max(R * Hc, 1), np.uint16), alt_offsets=np.zeros(R + 1, np.uint64), edges_by_alt=np.zeros(max(n_alts, 1), np.uint64),
+                 ref_pos=np.zeros(max(R, 1), np.uint64), edge_target_pos=np.zeros(max(n_edges, 1), np.uint64), overlaps=np.zeros(max(2 * n_ov, 1), np.uint64))
+        lib().orc_graph_trace_copy(self._h, _ptr(t["gt"]), _ptr(t["alt_offsets"]), _ptr(t["edges_by_alt"]), _ptr(t["ref_pos"]),
+                                   _ptr(t["edge_target_pos"]), _ptr(t["overlaps"]))
+        t["gt"] = t["gt"][: R * Hc].reshape(R, Hc) if Hc else np.zeros((R, 0), np.uint16)
+        t["edges_by_alt"], t["ref_pos"], t["edge_target_pos"] = t["edges_by_alt"][:n_alts], t["ref_pos"][:R], t["edge_target_pos"][:n_edges]
+        t["overlaps"] = t["overlaps"][: 2 * n_ov].reshape(n_ov, 2)
+        t["records"], t["copies"] = R, Hc
+        return t
 
     def labels(self):
         a = self.arrays()

@@ -14,7 +14,7 @@ BASES = "ACGT"
 
 
 def write_random_inputs(dirpath, seed, ref_len=200, n_records=30, n_samples=5, ploidy=2, overlap=True, sv=True,
-                        max_indel=6, alt_freq=0.3, long_del_prob=0.0, chrom="1"):
+                        max_indel=6, alt_freq=0.3, long_del_prob=0.0, chrom="1", many_alts_prob=0.0):
     rng = np.random.default_rng(seed)
     ref = "".join(rng.choice(list(BASES), ref_len))
     fa = os.path.join(dirpath, f"r{seed}.fa")
@@ -43,6 +43,8 @@ def write_random_inputs(dirpath, seed, ref_len=200, n_records=30, n_samples=5, p
         ref_span = max(1, min(ref_span, ref_len - pos))
         ref_allele = ref[pos : pos + ref_span]
         n_alts = 1 + int(rng.random() < 0.3) + int(rng.random() < 0.1)
+        if many_alts_prob and rng.random() < many_alts_prob:
+            n_alts = int(rng.integers(5, 10))
         alts = []
         for _ in range(n_alts):
             r = rng.random()

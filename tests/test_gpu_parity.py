@@ -519,6 +519,51 @@ def test_cut_positions_degenerate(v2m, tmp_path):
     _check_cuts(og, dg, 10, "no edges md 10")
 
 
+# ---- K5: path bits from parsed GT fields (variant_graph.cc:379-425) ---------------------------------------------------------
+def _check_ingest(v2m, og, label=""):
+    a, t = og.arrays(), og.genotype_trace()
+    words, ov = v2m.paths_from_genotypes(t["gt"], t["alt_offsets"], t["edges_by_alt"], a["h_pad"], a["e_pad"], t["ref_pos"], t["edge_target_pos"])
+    assert np.array_equal(words, a["paths_ec"]), label
+    assert ov.tolist() == t["overlaps"].tolist(), (label, ov.tolist(), t["overlaps"].tolist())
+    words2, none = v2m.paths_from_genotypes(t["gt"], t["alt_offsets"], t["edges_by_alt"], a["h_pad"], a["e_pad"])
+    assert none is None and np.array_equal(words2, words)
+    return len(ov)
+
+
+def test_ingest_genotypes_on_reference_fixtures(v2m, expected, golden_dir):
+    """The path matrices behind the node / edge tables of tests/variant_graph.cc:249-338 and the founder fixtures, rebuilt on the
+    device from the GT values the (restated) builder saw."""
+    import glob
+    n = 0
+    for vcf in sorted(glob.glob(os.path.join(golden_dir, "*", "*.vcf"))):
+        fa = vcf[:-4] + ".fa"
+        if not os.path.exists(fa):
+            fa = os.path.join(os.path.dirname(vcf), "test-1.fa")
+        og = orc.Graph.from_files(fa, vcf, "1")
+        _check_ingest(v2m, og, vcf)
+        n += 1
+    assert n >= 8
+
+
+def test_ingest_genotypes_random_graphs(v2m, tmp_path):
+    """Multi-allelic sites, unhandled SV ALTs (no edge), null alleles, overlapping ALTs within a chromosome copy (reported),
+    more than 1,024 chromosome copies (several warp blocks per record) and more than 4 ALTs per record."""
+    overlaps = 0
+    for seed in range(10):
+        og = rg.random_oracle_graph(str(tmp_path), 3100 + seed, ref_len=1200, n_records=80 + 30 * seed, n_samples=2 + 70 * seed, ploidy=1 + seed % 3,
+                                    overlap=bool(seed % 2), sv=bool(seed % 3 != 1), alt_freq=0.05 + 0.04 * seed, many_alts_prob=0.1)
+        overlaps += _check_ingest(v2m, og, f"seed {seed}")
+    assert overlaps > 0
+
+
+def test_ingest_genotypes_rejects_bad_allele(v2m):
+    gt = np.array([[0, 2, 0, 0]], np.uint16)            # ALT 2 of a record with one ALT
+    with pytest.raises(v2m.V2MError):
+        v2m.paths_from_genotypes(gt, [0, 1], [0], 64, 64)
+    words, _ = v2m.paths_from_genotypes(np.array([[0, 1, v2m.GT_NULL, 1]], np.uint16), [0, 1], [v2m.EDGE_MAX], 64, 64)
+    assert not words.any()                               # the only ALT has no edge
+
+
 # ---- C++ host adapters (vcf2multialign_b200/host/v2m_b200.hh) ------------------------------------------------------------
 @pytest.mark.parametrize("fa,vcf", [("founder-sequences/test-1.fa", "founder-sequences/test-1.vcf"), ("founder-sequences/test-1-2.fa", "founder-sequences/test-1.vcf"),
                                     ("founder-sequences/test-2.fa", "founder-sequences/test-2.vcf"), ("founder-sequences/test-3.fa", "founder-sequences/test-3.vcf"),

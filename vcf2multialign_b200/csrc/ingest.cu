@@ -1,0 +1,294 @@
+// K5 — genotype ingestion: the "Paths" loop of build_variant_graph (libvcf2multialign/variant_graph.cc:379-425), the step
+// that produces paths_by_edge_and_chrom_copy from the parsed GT fields.
+//
+// What the reference does per handled record, restated: every included chromosome copy (output row index
+// ploidy_csum[sample] + copy) whose GT allele a is neither 0 nor NULL_ALLELE and whose ALT has an edge
+// (edges_by_alt[a - 1] != EDGE_MAX; only plain and <DEL> ALTs get one, :328-364) sets bit (row, edge) (:424). Every ALT gets
+// a fresh edge (variant_graph::add_edge), so an edge column belongs to exactly one (record, ALT) pair. Independently, per
+// chromosome copy and in record order, an overlap is reported when the record starts before the target of the copy's
+// previous ALT edge (:405-418); the report does not change the bits.
+//
+// Kernels:
+//   ingest_genotypes_kernel   one warp per (record, 1024 chromosome copies): 32 coalesced 64-byte loads of GT values; for each
+//                             ALT of the record a ballot per load gives one 32-bit word of that ALT's edge column, lane k
+//                             keeps word k, and the column piece goes out as one 128-byte store. Algorithmic bytes:
+//                             2 · records · H read + E · H_pad / 8 written. Roofline: HBM read.
+//   genotype_overlaps_kernel  one thread per chromosome copy walks the records (loads coalesced across copies) and appends
+//                             (record, row) pairs; state (the copy's current target position) is kept between record blocks.
+#include <algorithm>
+#include <limits>
+#include <vector>
+
+#include "../../include/v2m_cuda.h"
+#include "common.cuh"
+
+namespace v2m {
+
+constexpr unsigned short GT_NULL = 0xffffu;						// V2M_GT_NULL
+constexpr u64 EDGE_NONE = 0xffffffffffffffffull;				// variant_graph::EDGE_MAX
+
+__global__ void __launch_bounds__(256)
+ingest_genotypes_kernel(unsigned short const * __restrict__ gt, u64 const n_records, u32 const H,
+	u64 const * __restrict__ alt_offsets /* [n_records + 1], relative to edges_by_alt */, u64 const * __restrict__ edges_by_alt,
+	u32 const Wh32 /* h_pad / 32 */, u32 const blocks_per_record, u64 const e_pad, u32 * __restrict__ paths32, u32 * __restrict__ bad)
+{
+	unsigned const lane(threadIdx.x & 31);
+	u64 const warp_id((u64(blockIdx.x) * blockDim.x + threadIdx.x) >> 5);
+	u64 const r(warp_id / blocks_per_record);
+	u32 const wb(u32(warp_id % blocks_per_record));
+	if (r >= n_records) return;
+	u64 const a0(alt_offsets[r]);
+	u32 const n_alts(u32(alt_offsets[r + 1] - a0));
+	unsigned short const *row(gt + r * H);
+	u32 const word_mine(wb * 32 + lane);
+
+	for (u32 base(0); base < max(n_alts, 1u); base += 4)
+	{
+		u32 const n(min(4u, n_alts - min(n_alts, base)));
+		u32 w[4] = {0, 0, 0, 0};
+#pragma unroll 4
+		for (u32 k = 0; k < 32; ++k)
+		{
+			u32 const h((wb * 32 + k) * 32 + lane);
+			u32 const g(h < H ? row[h] : 0u);
+			if (0 == base && 0 != g && GT_NULL != g && g > n_alts) atomicOr(bad, 1u);		// the reference asserts (:399)
+#pragma unroll
+			for (u32 j = 0; j < 4; ++j)
+				if (j < n)
+				{
+					u32 const b(__ballot_sync(0xffffffffu, g == base + j + 1));
+					if (lane == k) w[j] = b;
+				}
+		}
+		if (word_mine < Wh32)
+#pragma unroll
+			for (u32 j = 0; j < 4; ++j)
+			{
+				if (j >= n) break;
+				u64 const edge(edges_by_alt[a0 + base + j]);
+				if (EDGE_NONE == edge) continue;
+				if (edge >= e_pad) { atomicOr(bad, 2u); continue; }
+				paths32[edge * Wh32 + word_mine] = w[j];
+			}
+	}
+}
+
+
+__global__ void __launch_bounds__(128)
+genotype_overlaps_kernel(unsigned short const * __restrict__ gt, u64 const n_records, u64 const first_record, u32 const H,
+	u64 const * __restrict__ alt_offsets, u64 const * __restrict__ edges_by_alt,
+	u64 const * __restrict__ record_ref_pos, u64 const * __restrict__ edge_target_pos, u64 const n_edges,
+	u64 * __restrict__ target_by_copy, u64 * __restrict__ out_pairs, u64 const cap, unsigned long long * __restrict__ out_count)
+{
+	u32 const h(blockIdx.x * blockDim.x + threadIdx.x);
+	if (h >= H) return;
+	u64 target(target_by_copy[h]);
+	constexpr int U = 8;
+	for (u64 r0(0); r0 < n_records; r0 += U)
+	{
+		u32 g[U];
+#pragma unroll
+		for (int u = 0; u < U; ++u)
+			g[u] = (r0 + u < n_records) ? gt[(r0 + u) * H + h] : 0u;
+#pragma unroll
+		for (int u = 0; u < U; ++u)
+		{
+			if (0 == g[u] || GT_NULL == g[u]) continue;
+			u64 const r(r0 + u);
+			u64 const a0(alt_offsets[r]);
+			if (g[u] > alt_offsets[r + 1] - a0) continue;					// reported by the ingest kernel
+			u64 const edge(edges_by_alt[a0 + g[u] - 1]);
+			if (EDGE_NONE == edge || edge >= n_edges) continue;
+			if (record_ref_pos[r] < target)
+			{
+				unsigned long long const slot(atomicAdd(out_count, 1ull));
+				if (slot < cap) { out_pairs[2 * slot] = first_record + r; out_pairs[2 * slot + 1] = h; }
+			}
+			target = edge_target_pos[edge];
+		}
+	}
+	target_by_copy[h] = target;
+}
+
+namespace {
+	struct dbuf
+	{
+		void *p{};
+		~dbuf() { if (p) cudaFree(p); }
+		int alloc(u64 bytes) { V2M_CUDA_TRY(cudaMalloc(&p, std::max<u64>(bytes, 16))); return 0; }
+		template <typename T> T *as() const { return static_cast<T *>(p); }
+	};
+}
+
+// Core: fills d_paths (device, e_pad × h_pad / 64 words, zeroed here). gt is host memory and is streamed in record blocks.
+int paths_from_genotypes_device(unsigned short const *gt, u64 const n_records, u32 const H, u64 const *alt_offsets, u64 const *edges_by_alt,
+	u64 const *record_ref_pos, u64 const *edge_target_pos, u64 const n_edges, u64 const h_pad, u64 const e_pad, void *d_paths,
+	std::vector<u64> *overlaps, float *kernel_ms)
+{
+	if (0 != h_pad % 64 || 0 != e_pad % 64 || h_pad < H) return fail(V2M_ERR_ARGUMENT, "paths_from_genotypes: path matrix dimensions must be multiples of 64 covering all chromosome copies");
+	if (n_records && (!gt || !alt_offsets)) return fail(V2M_ERR_ARGUMENT, "paths_from_genotypes: NULL argument");
+	u64 const n_alts(n_records ? alt_offsets[n_records] : 0);
+	if (n_alts && !edges_by_alt) return fail(V2M_ERR_ARGUMENT, "paths_from_genotypes: NULL edges_by_alt");
+	bool const want_overlaps(overlaps && record_ref_pos && edge_target_pos);
+	if (overlaps) overlaps->clear();
+	V2M_CUDA_TRY(cudaMemset(d_paths, 0, e_pad * h_pad / 8));
+	if (0 == n_records || 0 == H) return V2M_OK;
+
+	u32 const Wh32(u32(h_pad / 32));
+	u32 const blocks_per_record((Wh32 + 31) / 32);
+	u64 const block_records(std::max<u64>(1, std::min<u64>(n_records, (u64(256) << 20) / (u64(H) * 2))));		// ~256 MB of GT values per block
+
+	dbuf d_gt[2], d_off, d_eba, d_ref, d_tgt, d_state, d_pairs, d_count, d_bad;
+	if (d_gt[0].alloc(block_records * H * 2) || d_gt[1].alloc(block_records * H * 2) || d_off.alloc((n_records + 1) * 8) || d_eba.alloc(n_alts * 8) || d_bad.alloc(4))
+		return V2M_ERR_CUDA;
+	V2M_CUDA_TRY(cudaMemcpy(d_off.p, alt_offsets, (n_records + 1) * 8, cudaMemcpyHostToDevice));
+	if (n_alts) V2M_CUDA_TRY(cudaMemcpy(d_eba.p, edges_by_alt, n_alts * 8, cudaMemcpyHostToDevice));
+	V2M_CUDA_TRY(cudaMemset(d_bad.p, 0, 4));
+	u64 pair_cap(0);
+	if (want_overlaps)
+	{
+		pair_cap = std::max<u64>(1024, n_records / 4);
+		if (d_ref.alloc(n_records * 8) || d_tgt.alloc(n_edges * 8) || d_state.alloc(u64(H) * 8) || d_pairs.alloc(pair_cap * 16) || d_count.alloc(8)) return V2M_ERR_CUDA;
+		V2M_CUDA_TRY(cudaMemcpy(d_ref.p, record_ref_pos, n_records * 8, cudaMemcpyHostToDevice));
+		if (n_edges) V2M_CUDA_TRY(cudaMemcpy(d_tgt.p, edge_target_pos, n_edges * 8, cudaMemcpyHostToDevice));
+	}
+
+	cudaStream_t streams[2];
+	cudaEvent_t ev0, ev1;
+	for (auto &s : streams) V2M_CUDA_TRY(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
+	V2M_CUDA_TRY(cudaEventCreate(&ev0)); V2M_CUDA_TRY(cudaEventCreate(&ev1));
+	struct guard_t { cudaStream_t *s; cudaEvent_t a, b; ~guard_t() { cudaStreamDestroy(s[0]); cudaStreamDestroy(s[1]); cudaEventDestroy(a); cudaEventDestroy(b); } } const guard{streams, ev0, ev1};
+	float ms_total(0);
+
+	for (int attempt(0); attempt < 2; ++attempt)
+	{
+		if (want_overlaps)
+		{
+			V2M_CUDA_TRY(cudaMemset(d_state.p, 0, u64(H) * 8));
+			V2M_CUDA_TRY(cudaMemset(d_count.p, 0, 8));
+		}
+		V2M_CUDA_TRY(cudaDeviceSynchronize());
+		int k(0);
+		for (u64 r0(0); r0 < n_records; r0 += block_records, k ^= 1)
+		{
+			u64 const nr(std::min(block_records, n_records - r0));
+			cudaStream_t const st(streams[k]);
+			// The two streams alternate; the overlap kernel carries state from block to block, so block b waits for block b - 1.
+			V2M_CUDA_TRY(cudaMemcpyAsync(d_gt[k].p, gt + r0 * H, nr * H * 2, cudaMemcpyHostToDevice, st));
+			V2M_CUDA_TRY(cudaEventRecord(ev0, st));
+			if (0 == attempt)
+			{
+				u64 const warps(nr * blocks_per_record);
+				ingest_genotypes_kernel<<<unsigned((warps * 32 + 255) / 256), 256, 0, st>>>(d_gt[k].as<unsigned short>(), nr, H, d_off.as<u64>() + r0, d_eba.as<u64>(),
+					Wh32, blocks_per_record, e_pad, static_cast<u32 *>(d_paths), d_bad.as<u32>());
+				V2M_CHECK_LAUNCH("ingest_genotypes_kernel");
+			}
+			if (want_overlaps)
+			{
+				V2M_CUDA_TRY(cudaStreamWaitEvent(st, ev1, 0));
+				genotype_overlaps_kernel<<<(H + 127) / 128, 128, 0, st>>>(d_gt[k].as<unsigned short>(), nr, r0, H, d_off.as<u64>() + r0, d_eba.as<u64>(),
+					d_ref.as<u64>() + r0, d_tgt.as<u64>(), n_edges, d_state.as<u64>(), d_pairs.as<u64>(), pair_cap, d_count.as<unsigned long long>());
+				V2M_CHECK_LAUNCH("genotype_overlaps_kernel");
+			}
+			V2M_CUDA_TRY(cudaEventRecord(ev1, st));
+			V2M_CUDA_TRY(cudaStreamSynchronize(st));			// pageable source: the copy was staged synchronously anyway
+			float ms(0);
+			cudaEventElapsedTime(&ms, ev0, ev1);
+			ms_total += ms;
+		}
+		u32 bad(0);
+		V2M_CUDA_TRY(cudaMemcpy(&bad, d_bad.p, 4, cudaMemcpyDeviceToHost));
+		if (bad & 1u) return fail(V2M_ERR_ARGUMENT, "paths_from_genotypes: a genotype refers to an ALT its record does not have (the reference asserts, variant_graph.cc:399)");
+		if (bad & 2u) return fail(V2M_ERR_ARGUMENT, "paths_from_genotypes: edge index beyond e_pad");
+		if (!want_overlaps) break;
+		unsigned long long count(0);
+		V2M_CUDA_TRY(cudaMemcpy(&count, d_count.p, 8, cudaMemcpyDeviceToHost));
+		if (count <= pair_cap)
+		{
+			overlaps->resize(2 * count);
+			if (count) V2M_CUDA_TRY(cudaMemcpy(overlaps->data(), d_pairs.p, count * 16, cudaMemcpyDeviceToHost));
+			// The reference reports in record order, then in output row order within the record.
+			std::vector<std::pair<u64, u64>> pairs(count);
+			for (u64 i(0); i < count; ++i) pairs[i] = {(*overlaps)[2 * i], (*overlaps)[2 * i + 1]};
+			std::sort(pairs.begin(), pairs.end());
+			for (u64 i(0); i < count; ++i) { (*overlaps)[2 * i] = pairs[i].first; (*overlaps)[2 * i + 1] = pairs[i].second; }
+			break;
+		}
+		if (attempt) return fail(V2M_ERR_STATE, "paths_from_genotypes: overlap list overflow after resizing");
+		pair_cap = count;
+		cudaFree(d_pairs.p); d_pairs.p = nullptr;
+		if (d_pairs.alloc(pair_cap * 16)) return V2M_ERR_CUDA;
+	}
+	if (kernel_ms) *kernel_ms = ms_total;
+	return V2M_OK;
+}
+
+} // namespace v2m
+
+
+extern "C" int v2m_cuda_paths_from_genotypes_device(const uint16_t *gt, uint64_t n_records, uint32_t n_copies,
+	const uint64_t *alt_offsets, const uint64_t *edges_by_alt, const uint64_t *record_ref_pos, const uint64_t *edge_target_pos, uint64_t n_edges,
+	uint64_t h_pad, uint64_t e_pad, void *d_paths, uint64_t *overlaps, uint64_t overlap_cap, uint64_t *n_overlaps)
+{
+	using namespace v2m;
+	if (!d_paths) return fail(V2M_ERR_ARGUMENT, "paths_from_genotypes: NULL output");
+	std::vector<u64> ov;
+	bool const want(nullptr != n_overlaps);
+	if (int const st = paths_from_genotypes_device(gt, n_records, n_copies, alt_offsets, edges_by_alt, record_ref_pos, edge_target_pos, n_edges,
+			h_pad, e_pad, d_paths, want ? &ov : nullptr, nullptr)) return st;
+	if (want)
+	{
+		*n_overlaps = ov.size() / 2;
+		if (ov.size() / 2 > overlap_cap || (!overlaps && !ov.empty()))
+			return fail(V2M_ERR_ARGUMENT, "paths_from_genotypes: overlap capacity too small (needed count is in *n_overlaps)");
+		std::copy(ov.begin(), ov.end(), overlaps);
+	}
+	return V2M_OK;
+}
+
+extern "C" int v2m_cuda_paths_from_genotypes(const uint16_t *gt, uint64_t n_records, uint32_t n_copies,
+	const uint64_t *alt_offsets, const uint64_t *edges_by_alt, const uint64_t *record_ref_pos, const uint64_t *edge_target_pos, uint64_t n_edges,
+	uint64_t h_pad, uint64_t e_pad, uint64_t *paths_by_edge_and_chrom_copy, uint64_t *overlaps, uint64_t overlap_cap, uint64_t *n_overlaps)
+{
+	using namespace v2m;
+	u64 const bytes(e_pad * h_pad / 8);
+	if (bytes && !paths_by_edge_and_chrom_copy) return fail(V2M_ERR_ARGUMENT, "paths_from_genotypes: NULL output");
+	void *d_paths(nullptr);
+	V2M_CUDA_TRY(cudaMalloc(&d_paths, std::max<u64>(bytes, 16)));
+	int st(v2m_cuda_paths_from_genotypes_device(gt, n_records, n_copies, alt_offsets, edges_by_alt, record_ref_pos, edge_target_pos, n_edges,
+		h_pad, e_pad, d_paths, overlaps, overlap_cap, n_overlaps));
+	if (!st && bytes && cudaSuccess != cudaMemcpy(paths_by_edge_and_chrom_copy, d_paths, bytes, cudaMemcpyDeviceToHost))
+		st = fail(V2M_ERR_CUDA, "paths_from_genotypes: D2H copy failed");
+	cudaFree(d_paths);
+	return st;
+}
+
+// Measurement hook: mean device time of `iters` launches of ingest_genotypes_kernel on GT values already resident in HBM.
+extern "C" int v2m_cuda_time_ingest_genotypes(const void *d_gt, uint64_t n_records, uint32_t n_copies, const void *d_alt_offsets, const void *d_edges_by_alt,
+	uint64_t h_pad, uint64_t e_pad, void *d_paths, int iters, float *ms_mean)
+{
+	using namespace v2m;
+	if (!d_gt || !d_alt_offsets || !d_edges_by_alt || !d_paths || !ms_mean || iters < 1) return fail(V2M_ERR_ARGUMENT, "time_ingest_genotypes: bad argument");
+	u32 const Wh32(u32(h_pad / 32)), blocks_per_record((Wh32 + 31) / 32);
+	u32 *d_bad(nullptr);
+	V2M_CUDA_TRY(cudaMalloc(reinterpret_cast<void **>(&d_bad), 4));
+	V2M_CUDA_TRY(cudaMemset(d_bad, 0, 4));
+	cudaEvent_t e0, e1;
+	V2M_CUDA_TRY(cudaEventCreate(&e0)); V2M_CUDA_TRY(cudaEventCreate(&e1));
+	u64 const warps(n_records * blocks_per_record);
+	cudaEventRecord(e0, nullptr);
+	for (int i(0); i < iters; ++i)
+	{
+		ingest_genotypes_kernel<<<unsigned((warps * 32 + 255) / 256), 256>>>(static_cast<unsigned short const *>(d_gt), n_records, n_copies,
+			static_cast<u64 const *>(d_alt_offsets), static_cast<u64 const *>(d_edges_by_alt), Wh32, blocks_per_record, e_pad, static_cast<u32 *>(d_paths), d_bad);
+		count_launch();
+	}
+	cudaEventRecord(e1, nullptr);
+	cudaError_t const err(cudaEventSynchronize(e1));
+	float ms(0);
+	cudaEventElapsedTime(&ms, e0, e1);
+	cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(d_bad);
+	if (cudaSuccess != err) return fail(V2M_ERR_CUDA, std::string("time_ingest_genotypes: ") + cudaGetErrorString(err));
+	*ms_mean = ms / float(iters);
+	return V2M_OK;
+}

@@ -237,3 +237,35 @@ class Plan:
         blob = b"".join(i.encode() + b"\0" for i in ids)
         cb = _lib.ROW_CALLBACK(lambda r, ctx: row_done(r)) if row_done else C.cast(None, _lib.ROW_CALLBACK)
         check(lib().v2m_cuda_write_a2m(self._p, blob, int(unaligned), fd, cb, None))
+
+
+GT_NULL = 0xFFFF
+EDGE_MAX = 0xFFFFFFFFFFFFFFFF
+
+
+def paths_from_genotypes(gt, alt_offsets, edges_by_alt, h_pad: int, e_pad: int, record_ref_pos=None, edge_target_pos=None):
+    """The "Paths" loop of build_variant_graph (variant_graph.cc:379-425) on the device (K5): gt is records × chromosome copies
+    (GT allele per output row; GT_NULL = '.'), ALT a of record r has edge edges_by_alt[alt_offsets[r] + a - 1] (EDGE_MAX: none).
+    Returns (words of paths_by_edge_and_chrom_copy, overlaps) with overlaps a k × 2 array of (record, row) in the
+    reference's reporting order, or None when the positions needed to detect them were not given."""
+    gt = np.ascontiguousarray(gt, dtype=np.uint16)
+    R, Hc = (gt.shape if gt.ndim == 2 else (0, 0))
+    off = np.ascontiguousarray(alt_offsets, dtype=np.uint64)
+    eba = np.ascontiguousarray(edges_by_alt, dtype=np.uint64)
+    out = np.zeros(max(h_pad * e_pad // 64, 1), np.uint64)
+    want = record_ref_pos is not None and edge_target_pos is not None
+    rp = np.ascontiguousarray(record_ref_pos, dtype=np.uint64) if want else None
+    tp = np.ascontiguousarray(edge_target_pos, dtype=np.uint64) if want else None
+    n_edges = int(tp.size) if want else 0
+    cap = 1024
+    while True:
+        ov = np.zeros(2 * cap, np.uint64)
+        n = C.c_uint64(0)
+        st = lib().v2m_cuda_paths_from_genotypes(ptr(gt), R, Hc, ptr(off), ptr(eba) if eba.size else None, ptr(rp), ptr(tp), n_edges, h_pad, e_pad,
+                                                  ptr(out), ptr(ov) if want else None, cap if want else 0, C.byref(n) if want else None)
+        if st != 0 and want and n.value > cap:
+            cap = int(n.value)
+            continue
+        check(st)
+        break
+    return out[: h_pad * e_pad // 64], (ov[: 2 * n.value].reshape(-1, 2) if want else None)
