@@ -394,4 +394,36 @@ double orc_time_transpose(u64 const *src, u64 rows, u64 cols, u64 *dst)
 	return std::chrono::duration<double>(t1 - t0).count();
 }
 
+// The "Paths" loop of build_variant_graph (variant_graph.cc:379-425, as restated in v2m_oracle.hh) alone, on a flat genotype
+// block: the CPU baseline of the device's genotype ingestion. One thread, as the reference. Returns seconds.
+double orc_time_paths_loop(std::uint16_t const *gt, u64 n_records, u32 copies, u64 const *alt_offsets, u64 const *edges_by_alt,
+	u64 const *ref_pos, u64 const *edge_target_pos, u64 h_pad, u64 e_pad, u64 *dst_words, u64 *n_overlaps)
+{
+	bit_matrix m(h_pad, e_pad);
+	std::vector<u64> target(copies, 0);
+	u64 overlaps(0);
+	auto const t0(std::chrono::steady_clock::now());
+	for (u64 r(0); r < n_records; ++r)
+	{
+		u64 const a0(alt_offsets[r]), n_alts(alt_offsets[r + 1] - a0);
+		std::uint16_t const *row(gt + r * copies);
+		for (u32 h(0); h < copies; ++h)
+		{
+			auto const alt_idx(row[h]);
+			if (0 == alt_idx) continue;
+			if (NULL_ALLELE == alt_idx) continue;
+			if (!(u64(alt_idx - 1) < n_alts)) continue;
+			u64 const edge_idx(edges_by_alt[a0 + alt_idx - 1]);
+			if (EDGE_MAX == edge_idx) continue;
+			if (ref_pos[r] < target[h]) ++overlaps;
+			target[h] = edge_target_pos[edge_idx];
+			m.set(h, edge_idx);
+		}
+	}
+	auto const t1(std::chrono::steady_clock::now());
+	if (dst_words) std::memcpy(dst_words, m.words.data(), m.words.size() * 8);
+	if (n_overlaps) *n_overlaps = overlaps;
+	return std::chrono::duration<double>(t1 - t0).count();
+}
+
 } // extern "C"

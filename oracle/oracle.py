@@ -47,6 +47,8 @@ def lib():
     L.orc_graph_from_arrays.argtypes = [u64, u64, vp, vp, vp, vp, vp, vp, vp, vp, u64, u64, u32, vp, cp, vp, u64]
     L.orc_graph_free.argtypes = [vp]
     L.orc_graph_dims.argtypes = [vp, vp]
+    L.orc_time_paths_loop.restype = C.c_double
+    L.orc_time_paths_loop.argtypes = [vp, u64, C.c_uint32, vp, vp, vp, vp, u64, u64, vp, vp]
     L.orc_graph_trace_dims.restype = None
     L.orc_graph_trace_dims.argtypes = [vp, vp]
     L.orc_graph_trace_copy.restype = None

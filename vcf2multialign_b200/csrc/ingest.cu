@@ -28,7 +28,7 @@ constexpr unsigned short GT_NULL = 0xffffu;						// V2M_GT_NULL
 constexpr u64 EDGE_NONE = 0xffffffffffffffffull;				// variant_graph::EDGE_MAX
 
 __global__ void __launch_bounds__(256)
-ingest_genotypes_kernel(unsigned short const * __restrict__ gt, u64 const n_records, u32 const H,
+ingest_genotypes_scalar_kernel(unsigned short const * __restrict__ gt, u64 const n_records, u32 const H,
 	u64 const * __restrict__ alt_offsets /* [n_records + 1], relative to edges_by_alt */, u64 const * __restrict__ edges_by_alt,
 	u32 const Wh32 /* h_pad / 32 */, u32 const blocks_per_record, u64 const e_pad, u32 * __restrict__ paths32, u32 * __restrict__ bad)
 {
@@ -71,6 +71,87 @@ ingest_genotypes_kernel(unsigned short const * __restrict__ gt, u64 const n_reco
 				paths32[edge * Wh32 + word_mine] = w[j];
 			}
 	}
+}
+
+
+// The same, for H % 8 == 0 (rows of GT values are then 16-byte aligned): each lane loads 8 GT values with one 128-bit load,
+// so a warp covers 256 chromosome copies per load and 1,024 with its four loads in flight together. Per ALT, a lane turns
+// its 8 values into 8 bits with packed 16-bit compares, four lanes OR their bytes into a word of the edge column (two
+// shuffles), one more shuffle hands word k to lane k, and the 32 words leave as one 128-byte store.
+// Bit 15 / bit 31 of the result are set iff the low / high 16-bit half of x equals the half-word replicated in `pattern`
+// (exact: the addition never carries out of the low 15 bits of a half).
+__device__ __forceinline__ u32 eq_halves(u32 const x, u32 const pattern)
+{
+	u32 const t(x ^ pattern);
+	return ~(((t & 0x7fff7fffu) + 0x7fff7fffu) | t) & 0x80008000u;
+}
+
+struct eq4 { u32 x, y, z, w; };
+__device__ __forceinline__ eq4 eq_halves4(uint4 const &v, u32 const pattern)
+{
+	return eq4{eq_halves(v.x, pattern), eq_halves(v.y, pattern), eq_halves(v.z, pattern), eq_halves(v.w, pattern)};
+}
+
+// The 8 result bits of one lane's 8 GT values (value t of the lane → bit t).
+__device__ __forceinline__ u32 gather8(eq4 const &m)
+{
+	u32 const r((m.x >> 15) | (m.y >> 13) | (m.z >> 11) | (m.w >> 9));		// low halves → bits 0, 2, 4, 6; high halves → 16, 18, 20, 22
+	return (r & 0x55u) | ((r >> 15) & 0xaau);
+}
+
+__global__ void __launch_bounds__(256)
+ingest_genotypes_kernel(unsigned short const * __restrict__ gt, u64 const n_records, u32 const H,
+	u64 const * __restrict__ alt_offsets, u64 const * __restrict__ edges_by_alt,
+	u32 const Wh32, u32 const blocks_per_record, u64 const e_pad, u32 * __restrict__ paths32, u32 * __restrict__ bad)
+{
+	unsigned const lane(threadIdx.x & 31);
+	u64 const warp_id((u64(blockIdx.x) * blockDim.x + threadIdx.x) >> 5);
+	u64 const r(warp_id / blocks_per_record);
+	u32 const wb(u32(warp_id % blocks_per_record));
+	if (r >= n_records) return;
+	u64 const a0(alt_offsets[r]);
+	u32 const n_alts(u32(alt_offsets[r + 1] - a0));
+	unsigned short const *row(gt + r * H);
+
+	uint4 v[4];
+#pragma unroll
+	for (int i = 0; i < 4; ++i)
+	{
+		u32 const h0(wb * 1024 + i * 256 + lane * 8);
+		v[i] = (h0 < H) ? ld_nc_v4(row + h0) : make_uint4(0, 0, 0, 0);
+	}
+	// :399 — every value must be 0, NULL or one of the record's ALTs: `known` collects the halves accounted for.
+	u32 known[4];
+#pragma unroll
+	for (int i = 0; i < 4; ++i)
+	{
+		eq4 const z(eq_halves4(v[i], 0u)), n(eq_halves4(v[i], 0xffffffffu));
+		// the four words' bits 15 / 31 packed into bits 0–3 / 16–19 of one register
+		known[i] = ((z.x | n.x) >> 15) | ((z.y | n.y) >> 14) | ((z.z | n.z) >> 13) | ((z.w | n.w) >> 12);
+	}
+	u32 const word_mine(wb * 32 + lane);
+	for (u32 a(0); a < n_alts; ++a)
+	{
+		u64 const edge(edges_by_alt[a0 + a]);
+		u32 const pattern((a + 1) | ((a + 1) << 16));
+		u32 mine(0);
+#pragma unroll
+		for (int i = 0; i < 4; ++i)
+		{
+			eq4 const m(eq_halves4(v[i], pattern));
+			known[i] |= (m.x >> 15) | (m.y >> 14) | (m.z >> 13) | (m.w >> 12);
+			u32 w(gather8(m) << (8 * (lane & 3)));
+			w |= __shfl_xor_sync(0xffffffffu, w, 1);
+			w |= __shfl_xor_sync(0xffffffffu, w, 2);						// lanes 4g … 4g+3 hold word 8i + g of the block
+			u32 const t(__shfl_sync(0xffffffffu, w, 4 * (lane & 7)));		// lane L reads word 8i + L % 8
+			if (int(lane >> 3) == i) mine = t;
+		}
+		if (EDGE_NONE == edge) continue;
+		if (edge >= e_pad) { atomicOr(bad, 2u); continue; }
+		if (word_mine < Wh32) paths32[edge * Wh32 + word_mine] = mine;
+	}
+	// bits 0–3 (low halves) and 16–19 (high halves) of known[i] must all be set
+	if (0x000f000fu != (known[0] & known[1] & known[2] & known[3] & 0x000f000fu)) atomicOr(bad, 1u);
 }
 
 
@@ -120,6 +201,18 @@ namespace {
 	};
 }
 
+namespace {
+	void launch_ingest(unsigned short const *d_gt, u64 nr, u32 H, u64 const *d_off, u64 const *d_eba, u32 Wh32, u64 e_pad, u32 *d_paths32, u32 *d_bad, cudaStream_t st)
+	{
+		bool const vec(0 == H % 8 && 0 == (reinterpret_cast<u64>(d_gt) & 15));
+		u32 const blocks_per_record((Wh32 + 31) / 32);			// 1,024 chromosome copies per warp in both kernels
+		u64 const warps(nr * blocks_per_record);
+		unsigned const ctas(unsigned((warps * 32 + 255) / 256));
+		if (vec) ingest_genotypes_kernel<<<ctas, 256, 0, st>>>(d_gt, nr, H, d_off, d_eba, Wh32, blocks_per_record, e_pad, d_paths32, d_bad);
+		else ingest_genotypes_scalar_kernel<<<ctas, 256, 0, st>>>(d_gt, nr, H, d_off, d_eba, Wh32, blocks_per_record, e_pad, d_paths32, d_bad);
+	}
+}
+
 // Core: fills d_paths (device, e_pad × h_pad / 64 words, zeroed here). gt is host memory and is streamed in record blocks.
 int paths_from_genotypes_device(unsigned short const *gt, u64 const n_records, u32 const H, u64 const *alt_offsets, u64 const *edges_by_alt,
 	u64 const *record_ref_pos, u64 const *edge_target_pos, u64 const n_edges, u64 const h_pad, u64 const e_pad, void *d_paths,
@@ -135,7 +228,6 @@ int paths_from_genotypes_device(unsigned short const *gt, u64 const n_records, u
 	if (0 == n_records || 0 == H) return V2M_OK;
 
 	u32 const Wh32(u32(h_pad / 32));
-	u32 const blocks_per_record((Wh32 + 31) / 32);
 	u64 const block_records(std::max<u64>(1, std::min<u64>(n_records, (u64(256) << 20) / (u64(H) * 2))));		// ~256 MB of GT values per block
 
 	dbuf d_gt[2], d_off, d_eba, d_ref, d_tgt, d_state, d_pairs, d_count, d_bad;
@@ -178,9 +270,7 @@ int paths_from_genotypes_device(unsigned short const *gt, u64 const n_records, u
 			V2M_CUDA_TRY(cudaEventRecord(ev0, st));
 			if (0 == attempt)
 			{
-				u64 const warps(nr * blocks_per_record);
-				ingest_genotypes_kernel<<<unsigned((warps * 32 + 255) / 256), 256, 0, st>>>(d_gt[k].as<unsigned short>(), nr, H, d_off.as<u64>() + r0, d_eba.as<u64>(),
-					Wh32, blocks_per_record, e_pad, static_cast<u32 *>(d_paths), d_bad.as<u32>());
+				launch_ingest(d_gt[k].as<unsigned short>(), nr, H, d_off.as<u64>() + r0, d_eba.as<u64>(), Wh32, e_pad, static_cast<u32 *>(d_paths), d_bad.as<u32>(), st);
 				V2M_CHECK_LAUNCH("ingest_genotypes_kernel");
 			}
 			if (want_overlaps)
@@ -269,18 +359,17 @@ extern "C" int v2m_cuda_time_ingest_genotypes(const void *d_gt, uint64_t n_recor
 {
 	using namespace v2m;
 	if (!d_gt || !d_alt_offsets || !d_edges_by_alt || !d_paths || !ms_mean || iters < 1) return fail(V2M_ERR_ARGUMENT, "time_ingest_genotypes: bad argument");
-	u32 const Wh32(u32(h_pad / 32)), blocks_per_record((Wh32 + 31) / 32);
+	u32 const Wh32(u32(h_pad / 32));
 	u32 *d_bad(nullptr);
 	V2M_CUDA_TRY(cudaMalloc(reinterpret_cast<void **>(&d_bad), 4));
 	V2M_CUDA_TRY(cudaMemset(d_bad, 0, 4));
 	cudaEvent_t e0, e1;
 	V2M_CUDA_TRY(cudaEventCreate(&e0)); V2M_CUDA_TRY(cudaEventCreate(&e1));
-	u64 const warps(n_records * blocks_per_record);
 	cudaEventRecord(e0, nullptr);
 	for (int i(0); i < iters; ++i)
 	{
-		ingest_genotypes_kernel<<<unsigned((warps * 32 + 255) / 256), 256>>>(static_cast<unsigned short const *>(d_gt), n_records, n_copies,
-			static_cast<u64 const *>(d_alt_offsets), static_cast<u64 const *>(d_edges_by_alt), Wh32, blocks_per_record, e_pad, static_cast<u32 *>(d_paths), d_bad);
+		launch_ingest(static_cast<unsigned short const *>(d_gt), n_records, n_copies, static_cast<u64 const *>(d_alt_offsets), static_cast<u64 const *>(d_edges_by_alt),
+			Wh32, e_pad, static_cast<u32 *>(d_paths), d_bad, nullptr);
 		count_launch();
 	}
 	cudaEventRecord(e1, nullptr);
