@@ -334,38 +334,51 @@ emit_rows_kernel(emit_params const p)
 #pragma unroll 1
 			for (u32 chunk(0); chunk < n_words; chunk += 32)
 			{
-				u64 word(0 == chunk ? w_cur : load_word(r, chunk + lane));
-				u64 const e_base(64 * (w_lo + chunk + lane));
-				bool pending(false);
-				edge_rec prec{};
-				u32 plo(0), phi(0);
+				u64 const word(0 == chunk ? w_cur : load_word(r, chunk + lane));		// lane ↔ taken word chunk + lane
+				unsigned nz(__ballot_sync(0xffffffffu, 0 != word));
 #pragma unroll 1
-				for (;;)
+				while (nz)
 				{
-					// Each lane applies the short patches of its word until it meets a long span (or runs out).
-					while (!pending && word)
+					// One non-empty word at a time, its 64 edges spread over the lanes: the row's patches in this word are
+					// applied side by side (taken edges of one row never overlap, so their order does not matter).
+					int const wl(__ffs(nz) - 1);
+					nz &= nz - 1;
+					u32 const bits_lo(__shfl_sync(0xffffffffu, u32(word), wl)), bits_hi(__shfl_sync(0xffffffffu, u32(word >> 32), wl));
+					u64 const e_base(64 * (w_lo + chunk + wl));
+#pragma unroll
+					for (int half = 0; half < 2; ++half)
 					{
-						int const b(__ffsll((long long) word) - 1);
-						word &= word - 1;
-						edge_rec const rec(*reinterpret_cast<edge_rec const *>(&reinterpret_cast<uint4 const *>(erecs)[e_base + b]));
-						u32 const lo(max(rec.a0, c0_32)), hi(min(rec.a1, c1_32));
-						if (lo >= hi) continue;
-						if (hi - lo <= K2_SHORT_PATCH)
-							for (u32 col(lo); col < hi; ++col) buf[col - t0_32] = patch_byte(rec, labels, col);
-						else { pending = true; prec = rec; plo = lo; phi = hi; }
+						u32 const bits(half ? bits_hi : bits_lo);
+						if (0 == bits) continue;
+						bool pending(false);
+						edge_rec prec{};
+						u32 plo(0), phi(0);
+						if (bits >> lane & 1u)
+						{
+							edge_rec const rec(*reinterpret_cast<edge_rec const *>(&reinterpret_cast<uint4 const *>(erecs)[e_base + 32 * half + lane]));
+							u32 const lo(max(rec.a0, c0_32)), hi(min(rec.a1, c1_32));
+							if (lo < hi)
+							{
+								if (hi - lo <= K2_SHORT_PATCH)
+									for (u32 col(lo); col < hi; ++col) buf[col - t0_32] = patch_byte(rec, labels, col);
+								else { pending = true; prec = rec; plo = lo; phi = hi; }
+							}
+						}
+						// Long spans (large deletions / insertions) are written by the whole warp, one at a time.
+						unsigned m(__ballot_sync(0xffffffffu, pending));
+						while (m)
+						{
+							int const l(__ffs(m) - 1);
+							m &= m - 1;
+							edge_rec rec;
+							rec.a0 = __shfl_sync(0xffffffffu, prec.a0, l);
+							rec.a1 = __shfl_sync(0xffffffffu, prec.a1, l);
+							rec.label_off = __shfl_sync(0xffffffffu, prec.label_off, l);
+							rec.label_len = __shfl_sync(0xffffffffu, prec.label_len, l);
+							u32 const lo(__shfl_sync(0xffffffffu, plo, l)), hi(__shfl_sync(0xffffffffu, phi, l));
+							for (u32 col(lo + lane); col < hi; col += 32) buf[col - t0_32] = patch_byte(rec, labels, col);
+						}
 					}
-					// Long spans (large deletions / insertions) are written by the whole warp, one at a time.
-					unsigned const m(__ballot_sync(0xffffffffu, pending));
-					if (0 == m) break;
-					int const l(__ffs(m) - 1);
-					edge_rec rec;
-					rec.a0 = __shfl_sync(0xffffffffu, prec.a0, l);
-					rec.a1 = __shfl_sync(0xffffffffu, prec.a1, l);
-					rec.label_off = __shfl_sync(0xffffffffu, prec.label_off, l);
-					rec.label_len = __shfl_sync(0xffffffffu, prec.label_len, l);
-					u32 const lo(__shfl_sync(0xffffffffu, plo, l)), hi(__shfl_sync(0xffffffffu, phi, l));
-					for (u32 col(lo + lane); col < hi; col += 32) buf[col - t0_32] = patch_byte(rec, labels, col);
-					if (int(lane) == l) pending = false;
 				}
 			}
 		}
