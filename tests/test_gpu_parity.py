@@ -564,6 +564,32 @@ def test_ingest_genotypes_rejects_bad_allele(v2m):
     assert not words.any()                               # the only ALT has no edge
 
 
+# ---- reference-format graph files → device rows --------------------------------------------------------------
+def test_rows_from_reference_format_graph_files(v2m, expected, golden_dir):
+    """A graph archive as a stock vcf2multialign writes it (--output-graph; here written by the real cereal headers) is loaded,
+    uploaded and materialised: founder A2M text identical to the reference's goldens, cut positions identical to the file's."""
+    from vcf2multialign_b200 import interchange as ic
+    for case in expected["founder_sequences"]:
+        stem = "founder-sequences_" + case["vcf"][:-4]
+        gp = os.path.join(golden_dir, "cereal", stem + ".graph")
+        if case["fa"][:-3] != case["vcf"][:-4]:
+            continue                                     # same VCF over another reference: a different graph (the sink moves)
+        g = ic.load_variant_graph(gp)
+        ref = orc.Graph.from_files(os.path.join(golden_dir, "founder-sequences", case["fa"]), os.path.join(golden_dir, "founder-sequences", case["vcf"]), "1").arrays()["ref"]
+        dg = v2m.DeviceGraph(g, ref)
+        file_cuts, md, score = ic.load_cut_positions(os.path.join(golden_dir, "cereal", stem + ".cuts"))
+        cuts, sc = dg.find_cut_positions(md)
+        assert cuts.tolist() == file_cuts.tolist() == case["cuts"] and sc == score
+        out = v2m.founder_sequence_greedy_output(None, True, False, False)
+        out.set_cut_positions(file_cuts)
+        assert out.find_matchings(dg, 2)
+        import tempfile
+        with tempfile.TemporaryDirectory() as td:
+            dst = os.path.join(td, "out.a2m")
+            out.output_a2m(None, dg, dst)
+            assert open(dst).read() == case["a2m"], case["vcf"]
+
+
 # ---- C++ host adapters (vcf2multialign_b200/host/v2m_b200.hh) ------------------------------------------------------------
 @pytest.mark.parametrize("fa,vcf", [("founder-sequences/test-1.fa", "founder-sequences/test-1.vcf"), ("founder-sequences/test-1-2.fa", "founder-sequences/test-1.vcf"),
                                     ("founder-sequences/test-2.fa", "founder-sequences/test-2.vcf"), ("founder-sequences/test-3.fa", "founder-sequences/test-3.vcf"),

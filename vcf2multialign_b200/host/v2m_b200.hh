@@ -522,6 +522,11 @@ public:
 	[[nodiscard]] cut_position_score_type max_segmentation_height() const { return m_score; }								// output.hh:124
 	// What load_cut_positions (--input-cut-positions) provides in the reference.
 	void set_cut_positions(cut_position_vector cuts) { m_cut_positions = std::move(cuts); }
+	void set_cut_positions(cut_position_vector cuts, std::uint64_t const min_distance, cut_position_score_type const score)
+	{
+		m_cut_positions = std::move(cuts); m_min_distance = min_distance; m_score = score;
+	}
+	[[nodiscard]] std::uint64_t minimum_distance() const { return m_min_distance; }
 
 	// output.hh:123, founder_sequence_greedy_output.cc:139-152 → find_initial_cut_positions_lambda_min (find_cut_positions.cc:93-211).
 	[[nodiscard]] bool find_cut_positions(sequence_type const &ref_seq, t_graph const &graph, std::uint64_t const minimum_distance)
