@@ -237,6 +237,58 @@ def test_haplotype_output_a2m_stream(v2m, tmp_path, chrom, output_ref):
         out.output_a2m(a["ref"], g, dst)    # O_CREAT|O_EXCL as lb::open_file_for_writing(CREATE)
 
 
+def test_write_a2m_sinks(v2m, tmp_path):
+    """v2m_cuda_write_a2m on a regular file opened read-write (filled through a shared mapping by several threads, starting at
+    the descriptor's position and leaving it at the end), on write-only and O_APPEND descriptors and on a pipe (sequential
+    writes): the same bytes every time."""
+    import threading
+    og = rg.random_oracle_graph(str(tmp_path), 777, ref_len=30000, n_records=900, n_samples=9, ploidy=2, long_del_prob=0.02)
+    dg, g = _device_graph(v2m, og)
+    H = og.dims()[4]
+    plan = dg.plan_haplotypes([v2m.PLOIDY_MAX] + list(range(H)))
+    ids = ["REF"] + [f"row{h}" for h in range(H)]
+    exp = b"".join(b">" + i.encode() + b"\n" + (og.output_sequence(orc.PLOIDY_MAX if k == 0 else k - 1)) + b"\n" for k, i in enumerate(ids))
+    for unaligned in (False, True):
+        e = exp if not unaligned else b"".join(b">" + i.encode() + b"\n" + og.output_sequence(orc.PLOIDY_MAX if k == 0 else k - 1, None, True) + b"\n" for k, i in enumerate(ids))
+        # regular file, not at offset 0: read-write (mapped) and write-only (sequential)
+        for mode in (os.O_RDWR, os.O_WRONLY):
+            p1 = str(tmp_path / f"a{int(unaligned)}{mode}.a2m")
+            fd = os.open(p1, mode | os.O_CREAT, 0o644)
+            os.write(fd, b"prefix\n")
+            done = []
+            plan.write_a2m(ids, fd, unaligned, row_done=done.append)
+            assert os.lseek(fd, 0, os.SEEK_CUR) == 7 + len(e)
+            os.write(fd, b"tail")
+            os.close(fd)
+            assert open(p1, "rb").read() == b"prefix\n" + e + b"tail"
+            assert done == list(range(H + 1))
+        # overwriting the middle of a longer file keeps what follows
+        p3 = str(tmp_path / f"c{int(unaligned)}.a2m")
+        open(p3, "wb").write(b"x" * (len(e) + 100))
+        fd = os.open(p3, os.O_RDWR)
+        os.lseek(fd, 10, os.SEEK_SET)
+        plan.write_a2m(ids, fd, unaligned)
+        os.close(fd)
+        assert open(p3, "rb").read() == b"x" * 10 + e + b"x" * 90
+        # O_APPEND
+        p2 = str(tmp_path / f"b{int(unaligned)}.a2m")
+        open(p2, "wb").write(b"head\n")
+        fd = os.open(p2, os.O_WRONLY | os.O_APPEND)
+        plan.write_a2m(ids, fd, unaligned)
+        os.close(fd)
+        assert open(p2, "rb").read() == b"head\n" + e
+        # pipe
+        r, w_ = os.pipe()
+        chunks = []
+        t = threading.Thread(target=lambda: [chunks.append(b) for b in iter(lambda: os.read(r, 1 << 20), b"")])
+        t.start()
+        plan.write_a2m(ids, w_, unaligned)
+        os.close(w_)
+        t.join()
+        os.close(r)
+        assert b"".join(chunks) == e
+
+
 def test_haplotype_output_separate(v2m, tmp_path):
     og = rg.random_oracle_graph(str(tmp_path), 99, ref_len=3000, n_records=200, n_samples=4, ploidy=2)
     a = og.arrays()

@@ -8,6 +8,10 @@
 #include <string>
 #include <vector>
 
+#include <fcntl.h>
+#include <sys/mman.h>
+#include <sys/stat.h>
+#include <thread>
 #include <unistd.h>
 
 #include "../../include/v2m_cuda.h"
@@ -628,12 +632,87 @@ namespace {
 
 static int fd_sink(const void *bytes, uint64_t n, void *ctx) { return write_all(*static_cast<int *>(ctx), bytes, size_t(n)); }
 
+namespace {
+	// Seekable destinations opened for reading and writing are filled through a shared mapping: write(2) / pwrite(2) into the
+	// page cache is one copy at a time per file (the inode's write lock; ~3 GB/s on tmpfs whatever the number of threads), far
+	// below what the device delivers, whereas copies into a mapping fault and fill pages on as many threads as there are
+	// pieces. Pipes, sockets, O_APPEND and write-only descriptors (output.cc:26-38 --pipe, …) stay on sequential write(2).
+	struct copy_piece { void *dst; void const *src; u64 n; };
+
+	struct file_mapping
+	{
+		int		fd{-1};
+		u8		*base{};		// mapping of [map_offset, map_offset + map_bytes) of the file
+		u64		map_offset{}, map_bytes{};
+		u64		position{};		// file offset of the next byte of the stream
+
+		bool open(int const fd_, u64 const stream_bytes)
+		{
+			struct stat sb;
+			if (0 != ::fstat(fd_, &sb) || !S_ISREG(sb.st_mode)) return false;
+			int const flags(::fcntl(fd_, F_GETFL));
+			if (-1 == flags || (flags & O_APPEND) || O_RDWR != (flags & O_ACCMODE)) return false;
+			off_t const pos(::lseek(fd_, 0, SEEK_CUR));
+			if (pos < 0 || 0 == stream_bytes) return false;
+			u64 const page(u64(::sysconf(_SC_PAGESIZE)));
+			u64 const end(u64(pos) + stream_bytes);
+			if (u64(sb.st_size) < end && 0 != ::ftruncate(fd_, off_t(end))) return false;
+			map_offset = u64(pos) / page * page;
+			map_bytes = end - map_offset;
+			void *m(::mmap(nullptr, map_bytes, PROT_READ | PROT_WRITE, MAP_SHARED, fd_, off_t(map_offset)));
+			if (MAP_FAILED == m)
+			{
+				if (u64(sb.st_size) < end) (void) ::ftruncate(fd_, sb.st_size);
+				return false;
+			}
+			fd = fd_; base = static_cast<u8 *>(m); position = u64(pos);
+			return true;
+		}
+
+		u8 *at(u64 const file_offset) const { return base + (file_offset - map_offset); }
+
+		int close(bool const ok)
+		{
+			if (!base) return V2M_OK;
+			::munmap(base, map_bytes);
+			base = nullptr;
+			if (ok && ::lseek(fd, off_t(position), SEEK_SET) < 0) return fail(V2M_ERR_STATE, std::string("lseek failed: ") + std::strerror(errno));
+			return V2M_OK;
+		}
+	};
+
+	void copy_parallel(std::vector<copy_piece> const &pieces, unsigned threads)
+	{
+		threads = std::max(1u, std::min<unsigned>(threads, unsigned(pieces.size())));
+		std::atomic<std::size_t> next{0};
+		auto const work([&]() {
+			for (;;)
+			{
+				std::size_t const i(next.fetch_add(1, std::memory_order_relaxed));
+				if (i >= pieces.size()) return;
+				std::memcpy(pieces[i].dst, pieces[i].src, pieces[i].n);
+			}
+		});
+		std::vector<std::thread> pool;
+		for (unsigned t(1); t < threads; ++t) pool.emplace_back(work);
+		work();
+		for (auto &th : pool) th.join();
+	}
+}
+
+static int stream_a2m_impl(v2m_plan_t p, const char *ids, int unaligned, v2m_sink sink, void *sink_ctx, v2m_row_callback row_done, void *ctx, int positional_fd);
+
 extern "C" int v2m_cuda_write_a2m(v2m_plan_t p, const char *ids, int unaligned, int fd, v2m_row_callback row_done, void *ctx)
 {
-	return v2m_cuda_stream_a2m(p, ids, unaligned, fd_sink, &fd, row_done, ctx);
+	return stream_a2m_impl(p, ids, unaligned, fd_sink, &fd, row_done, ctx, fd);
 }
 
 extern "C" int v2m_cuda_stream_a2m(v2m_plan_t p, const char *ids, int unaligned, v2m_sink sink, void *sink_ctx, v2m_row_callback row_done, void *ctx)
+{
+	return stream_a2m_impl(p, ids, unaligned, sink, sink_ctx, row_done, ctx, -1);
+}
+
+static int stream_a2m_impl(v2m_plan_t p, const char *ids, int unaligned, v2m_sink sink, void *sink_ctx, v2m_row_callback row_done, void *ctx, int const positional_fd)
 {
 	if (!p || !sink || (!ids && p->p.n_rows)) return fail(V2M_ERR_ARGUMENT, "stream_a2m: NULL argument");
 	device_graph const &g(*p->p.graph);
@@ -648,7 +727,18 @@ extern "C" int v2m_cuda_stream_a2m(v2m_plan_t p, const char *ids, int unaligned,
 	// block k + 1 is produced and copied. Rows keep a 16-byte pitch on the device; headers are interleaved here.
 	u64 const max_len(*std::max_element(lengths.begin(), lengths.end()));
 	u64 const pitch((std::max<u64>(max_len, 1) + 15) & ~u64(15));
-	u32 const block_rows(u32(std::max<u64>(1, std::min<u64>(n_rows, (u64(128) << 20) / pitch))));
+	u32 const block_rows(u32(std::max<u64>(1, std::min<u64>(n_rows, (u64(256) << 20) / pitch))));
+	file_mapping mapping;
+	bool positional(false);
+	if (positional_fd >= 0)
+	{
+		u64 total(0);
+		char const *id(ids);
+		for (u32 r(0); r < n_rows; ++r) { u64 const l(std::strlen(id)); total += 1 + l + 1 + lengths[r] + 1; id += l + 1; }
+		positional = mapping.open(positional_fd, total);
+	}
+	unsigned const writer_threads(std::max(1u, std::min(16u, std::thread::hardware_concurrency())));
+	std::vector<copy_piece> pieces;
 	u8 *h_buf[2] = {nullptr, nullptr};
 	u8 *d_buf[2] = {nullptr, nullptr};
 	cudaStream_t streams[2] = {nullptr, nullptr};
@@ -686,6 +776,29 @@ extern "C" int v2m_cuda_stream_a2m(v2m_plan_t p, const char *ids, int unaligned,
 			u32 const r1(std::min<u64>(n_rows, u64(r0) + block_rows));
 			if (r1 < n_rows && (st = produce(r1, k ^ 1))) break;
 			if (cudaSuccess != cudaStreamSynchronize(streams[k])) { st = fail(V2M_ERR_CUDA, std::string("write_a2m: ") + cudaGetErrorString(cudaGetLastError())); break; }
+			if (positional)
+			{
+				// The same bytes at the same file offsets as the sequential form below, copied into the mapping by several threads.
+				constexpr u64 piece_bytes(u64(4) << 20);
+				pieces.clear();
+				for (u32 r(r0); r < r1; ++r)
+				{
+					u64 const id_len(std::strlen(id));
+					u8 *dst(mapping.at(mapping.position));
+					dst[0] = '>'; std::memcpy(dst + 1, id, id_len); dst[1 + id_len] = '\n';
+					id += id_len + 1;
+					mapping.position += id_len + 2;
+					u8 const *row(h_buf[k] + u64(r - r0) * pitch);
+					for (u64 off(0); off < lengths[r]; off += piece_bytes)
+						pieces.push_back({mapping.at(mapping.position + off), row + off, std::min(piece_bytes, lengths[r] - off)});
+					mapping.position += lengths[r];
+					*mapping.at(mapping.position) = '\n';
+					mapping.position += 1;
+				}
+				copy_parallel(pieces, writer_threads);
+				if (row_done) for (u32 r(r0); r < r1; ++r) row_done(r, ctx);
+				continue;
+			}
 			for (u32 r(r0); r < r1 && !st; ++r)
 			{
 				// '>' id '\n' bytes '\n' (sequence_writer.cc:35-36; haplotype_output.cc:56-57, 75-76)
@@ -711,6 +824,8 @@ extern "C" int v2m_cuda_stream_a2m(v2m_plan_t p, const char *ids, int unaligned,
 		cudaFree(d_buf[i]);
 		if (h_buf[i]) cudaFreeHost(h_buf[i]);
 	}
+	// Leave the descriptor where sequential writes would have left it.
+	if (positional) { int const cst(mapping.close(V2M_OK == st)); if (!st) st = cst; }
 	return st;
 }
 

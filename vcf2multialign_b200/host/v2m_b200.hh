@@ -292,7 +292,7 @@ protected:
 		child = -1;
 		if (!m_pipe_cmd)
 		{
-			int const fd(::open(dst_name, O_WRONLY | O_CREAT | O_EXCL | O_CLOEXEC, 0644));
+			int const fd(::open(dst_name, O_RDWR | O_CREAT | O_EXCL | O_CLOEXEC, 0644));
 			if (fd < 0) throw error(std::string("unable to create ") + dst_name + ": " + std::strerror(errno));
 			return fd;
 		}

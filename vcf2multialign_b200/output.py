@@ -71,7 +71,7 @@ class output:
         dgraph = graph if isinstance(graph, DeviceGraph) else DeviceGraph(graph, ref_seq)
         plan, rows = self._rows(dgraph)
         own_fd = isinstance(dst, (str, bytes, os.PathLike))
-        fd = os.open(dst, os.O_WRONLY | os.O_CREAT | os.O_EXCL, 0o644) if own_fd else dst.fileno()
+        fd = os.open(dst, os.O_RDWR | os.O_CREAT | os.O_EXCL, 0o644) if own_fd else dst.fileno()
         if not own_fd:
             dst.flush()
         try:
@@ -118,7 +118,7 @@ class output:
                     if before:
                         before()
                     name = self._file_name(stem, should_include_fasta_header)
-                    fd = os.open(os.path.join(dst_dir, name), os.O_WRONLY | os.O_CREAT | os.O_EXCL, 0o644)
+                    fd = os.open(os.path.join(dst_dir, name), os.O_RDWR | os.O_CREAT | os.O_EXCL, 0o644)
                     with os.fdopen(fd, "wb") as f:
                         f.write(b">" + name.encode() + b"\n" + seq)
         finally:
