@@ -197,3 +197,47 @@ def test_c3_cut_positions_matchings_and_founder_rows(v2m, c2):
             hp = dg.plan_haplotypes([src])
             assert np.array_equal(plan.emit_rows(f, f + 1, c0, c1), hp.emit_rows(0, 1, c0, c1)), (f, s)
             hp.close()
+
+
+# ---- c4: the chr1 shape (249 Mbp, 6.3 M ALT edges, 5,008 chromosome copies; 1.25 TB of rows) ----------------------------------
+def test_c4_sampled_rows_vs_oracle(v2m):
+    """BASELINE.json's target shape: sampled rows byte for byte against the oracle, plus the row properties of the c2 test."""
+    from vcf2multialign_b200 import synth
+    from vcf2multialign_b200._lib import check, lib, ptr
+    w = synth.make_workload("c4", seed=1, with_paths=False)
+    g = w.graph
+    H, A = g.total_chromosome_copies(), g.aligned_length()
+    assert H == 5008 and A > 249_000_000
+    path_bytes = g.e_pad * g.h_pad // 8
+    d_paths = lib().v2m_cuda_device_alloc(path_bytes)
+    assert d_paths
+    try:
+        synth.path_bits_device(w, d_paths)
+        dg = v2m.DeviceGraph(g, w.ref, d_paths_by_edge_and_chrom_copy=d_paths)
+        We = g.e_pad // 64
+        sample = [3, 2504, 5007]
+        ce_all = dg.paths_by_chrom_copy_and_edge()
+        ce = np.zeros_like(ce_all)
+        for h in sample:
+            ce[h * We : (h + 1) * We] = ce_all[h * We : (h + 1) * We]
+        del ce_all
+        og = _oracle_from_workload(w, np.zeros(ce.size, np.uint64), ce)
+        del ce
+        plan = dg.plan_haplotypes([v2m.PLOIDY_MAX] + sample)
+        rows = plan.emit_rows()
+        assert rows.shape == (4, A)
+        assert rows[0].tobytes() == og.output_sequence(orc.PLOIDY_MAX)
+        for i, h in enumerate(sample):
+            assert rows[1 + i].tobytes() == og.output_sequence(h), h
+        lens = plan.row_lengths(True)
+        un = plan.emit_rows_unaligned()
+        for i in range(4):
+            nogap = rows[i][rows[i] != ord("-")].tobytes()
+            assert len(nogap) == int(lens[i]) and nogap == un[i], i
+        # a window across the 2^27 and 2^28 column marks and the ragged end
+        for c0, c1 in ((134_217_000, 134_218_500), (A - 4097, A)):
+            assert plan.emit_rows(2, 3, c0, c1)[0].tobytes() == rows[2][c0:c1].tobytes()
+        plan.close()
+        dg.close()
+    finally:
+        lib().v2m_cuda_device_free(d_paths)
