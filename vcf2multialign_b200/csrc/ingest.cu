@@ -16,7 +16,9 @@
 //   genotype_overlaps_kernel  one thread per chromosome copy walks the records (loads coalesced across copies) and appends
 //                             (record, row) pairs; state (the copy's current target position) is kept between record blocks.
 #include <algorithm>
+#include <cstring>
 #include <limits>
+#include <thread>
 #include <vector>
 
 #include "../../include/v2m_cuda.h"
@@ -216,7 +218,7 @@ namespace {
 // Core: fills d_paths (device, e_pad × h_pad / 64 words, zeroed here). gt is host memory and is streamed in record blocks.
 int paths_from_genotypes_device(unsigned short const *gt, u64 const n_records, u32 const H, u64 const *alt_offsets, u64 const *edges_by_alt,
 	u64 const *record_ref_pos, u64 const *edge_target_pos, u64 const n_edges, u64 const h_pad, u64 const e_pad, void *d_paths,
-	std::vector<u64> *overlaps, float *kernel_ms)
+	std::vector<u64> *overlaps)
 {
 	if (0 != h_pad % 64 || 0 != e_pad % 64 || h_pad < H) return fail(V2M_ERR_ARGUMENT, "paths_from_genotypes: path matrix dimensions must be multiples of 64 covering all chromosome copies");
 	if (n_records && (!gt || !alt_offsets)) return fail(V2M_ERR_ARGUMENT, "paths_from_genotypes: NULL argument");
@@ -228,7 +230,7 @@ int paths_from_genotypes_device(unsigned short const *gt, u64 const n_records, u
 	if (0 == n_records || 0 == H) return V2M_OK;
 
 	u32 const Wh32(u32(h_pad / 32));
-	u64 const block_records(std::max<u64>(1, std::min<u64>(n_records, (u64(256) << 20) / (u64(H) * 2))));		// ~256 MB of GT values per block
+	u64 const block_records(std::max<u64>(1, std::min<u64>(n_records, (u64(64) << 20) / (u64(H) * 2))));		// ~64 MB of GT values per block
 
 	dbuf d_gt[2], d_off, d_eba, d_ref, d_tgt, d_state, d_pairs, d_count, d_bad;
 	if (d_gt[0].alloc(block_records * H * 2) || d_gt[1].alloc(block_records * H * 2) || d_off.alloc((n_records + 1) * 8) || d_eba.alloc(n_alts * 8) || d_bad.alloc(4))
@@ -239,18 +241,36 @@ int paths_from_genotypes_device(unsigned short const *gt, u64 const n_records, u
 	u64 pair_cap(0);
 	if (want_overlaps)
 	{
-		pair_cap = std::max<u64>(1024, n_records / 4);
+		pair_cap = std::max<u64>(1024, n_records);
 		if (d_ref.alloc(n_records * 8) || d_tgt.alloc(n_edges * 8) || d_state.alloc(u64(H) * 8) || d_pairs.alloc(pair_cap * 16) || d_count.alloc(8)) return V2M_ERR_CUDA;
 		V2M_CUDA_TRY(cudaMemcpy(d_ref.p, record_ref_pos, n_records * 8, cudaMemcpyHostToDevice));
 		if (n_edges) V2M_CUDA_TRY(cudaMemcpy(d_tgt.p, edge_target_pos, n_edges * 8, cudaMemcpyHostToDevice));
 	}
 
+	// GT values arrive in pageable host memory: blocks are copied into two pinned buffers by a few threads and sent with
+	// asynchronous copies, so that the host copy of block b + 1 overlaps the transfer and the kernels of block b.
 	cudaStream_t streams[2];
-	cudaEvent_t ev0, ev1;
+	cudaEvent_t done[2];
+	unsigned short *h_gt[2] = {nullptr, nullptr};
 	for (auto &s : streams) V2M_CUDA_TRY(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
-	V2M_CUDA_TRY(cudaEventCreate(&ev0)); V2M_CUDA_TRY(cudaEventCreate(&ev1));
-	struct guard_t { cudaStream_t *s; cudaEvent_t a, b; ~guard_t() { cudaStreamDestroy(s[0]); cudaStreamDestroy(s[1]); cudaEventDestroy(a); cudaEventDestroy(b); } } const guard{streams, ev0, ev1};
-	float ms_total(0);
+	for (auto &e : done) V2M_CUDA_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+	struct guard_t
+	{
+		cudaStream_t *s; cudaEvent_t *e; unsigned short **h;
+		~guard_t() { for (int i(0); i < 2; ++i) { cudaStreamSynchronize(s[i]); cudaStreamDestroy(s[i]); cudaEventDestroy(e[i]); if (h[i]) cudaFreeHost(h[i]); } }
+	} const guard{streams, done, h_gt};
+	for (auto &h : h_gt)
+		if (cudaSuccess != cudaMallocHost(reinterpret_cast<void **>(&h), block_records * H * 2)) return fail(V2M_ERR_CUDA, "paths_from_genotypes: cudaMallocHost failed");
+	unsigned const copy_threads(std::max(1u, std::min(8u, std::thread::hardware_concurrency())));
+	auto const stage([&](unsigned short *dst, unsigned short const *src, u64 const bytes) {
+		u64 const piece((bytes / copy_threads + 4095) & ~u64(4095));
+		std::vector<std::thread> pool;
+		for (unsigned t(1); t < copy_threads; ++t)
+			if (u64(t) * piece < bytes)
+				pool.emplace_back([=]() { std::memcpy(reinterpret_cast<char *>(dst) + t * piece, reinterpret_cast<char const *>(src) + t * piece, std::min(piece, bytes - t * piece)); });
+		std::memcpy(dst, src, std::min(piece, bytes));
+		for (auto &th : pool) th.join();
+	});
 
 	for (int attempt(0); attempt < 2; ++attempt)
 	{
@@ -261,13 +281,14 @@ int paths_from_genotypes_device(unsigned short const *gt, u64 const n_records, u
 		}
 		V2M_CUDA_TRY(cudaDeviceSynchronize());
 		int k(0);
+		bool first(true);
 		for (u64 r0(0); r0 < n_records; r0 += block_records, k ^= 1)
 		{
 			u64 const nr(std::min(block_records, n_records - r0));
 			cudaStream_t const st(streams[k]);
-			// The two streams alternate; the overlap kernel carries state from block to block, so block b waits for block b - 1.
-			V2M_CUDA_TRY(cudaMemcpyAsync(d_gt[k].p, gt + r0 * H, nr * H * 2, cudaMemcpyHostToDevice, st));
-			V2M_CUDA_TRY(cudaEventRecord(ev0, st));
+			V2M_CUDA_TRY(cudaStreamSynchronize(st));			// buffers k are free again
+			stage(h_gt[k], gt + r0 * H, nr * H * 2);
+			V2M_CUDA_TRY(cudaMemcpyAsync(d_gt[k].p, h_gt[k], nr * H * 2, cudaMemcpyHostToDevice, st));
 			if (0 == attempt)
 			{
 				launch_ingest(d_gt[k].as<unsigned short>(), nr, H, d_off.as<u64>() + r0, d_eba.as<u64>(), Wh32, e_pad, static_cast<u32 *>(d_paths), d_bad.as<u32>(), st);
@@ -275,17 +296,17 @@ int paths_from_genotypes_device(unsigned short const *gt, u64 const n_records, u
 			}
 			if (want_overlaps)
 			{
-				V2M_CUDA_TRY(cudaStreamWaitEvent(st, ev1, 0));
+				// The overlap kernel carries per-copy state from block to block: block b follows block b - 1 (on the other stream).
+				if (!first) V2M_CUDA_TRY(cudaStreamWaitEvent(st, done[k ^ 1], 0));
 				genotype_overlaps_kernel<<<(H + 127) / 128, 128, 0, st>>>(d_gt[k].as<unsigned short>(), nr, r0, H, d_off.as<u64>() + r0, d_eba.as<u64>(),
 					d_ref.as<u64>() + r0, d_tgt.as<u64>(), n_edges, d_state.as<u64>(), d_pairs.as<u64>(), pair_cap, d_count.as<unsigned long long>());
 				V2M_CHECK_LAUNCH("genotype_overlaps_kernel");
 			}
-			V2M_CUDA_TRY(cudaEventRecord(ev1, st));
-			V2M_CUDA_TRY(cudaStreamSynchronize(st));			// pageable source: the copy was staged synchronously anyway
-			float ms(0);
-			cudaEventElapsedTime(&ms, ev0, ev1);
-			ms_total += ms;
+			V2M_CUDA_TRY(cudaEventRecord(done[k], st));
+			first = false;
 		}
+		V2M_CUDA_TRY(cudaStreamSynchronize(streams[0]));
+		V2M_CUDA_TRY(cudaStreamSynchronize(streams[1]));
 		u32 bad(0);
 		V2M_CUDA_TRY(cudaMemcpy(&bad, d_bad.p, 4, cudaMemcpyDeviceToHost));
 		if (bad & 1u) return fail(V2M_ERR_ARGUMENT, "paths_from_genotypes: a genotype refers to an ALT its record does not have (the reference asserts, variant_graph.cc:399)");
@@ -309,7 +330,6 @@ int paths_from_genotypes_device(unsigned short const *gt, u64 const n_records, u
 		cudaFree(d_pairs.p); d_pairs.p = nullptr;
 		if (d_pairs.alloc(pair_cap * 16)) return V2M_ERR_CUDA;
 	}
-	if (kernel_ms) *kernel_ms = ms_total;
 	return V2M_OK;
 }
 
@@ -325,7 +345,7 @@ extern "C" int v2m_cuda_paths_from_genotypes_device(const uint16_t *gt, uint64_t
 	std::vector<u64> ov;
 	bool const want(nullptr != n_overlaps);
 	if (int const st = paths_from_genotypes_device(gt, n_records, n_copies, alt_offsets, edges_by_alt, record_ref_pos, edge_target_pos, n_edges,
-			h_pad, e_pad, d_paths, want ? &ov : nullptr, nullptr)) return st;
+			h_pad, e_pad, d_paths, want ? &ov : nullptr)) return st;
 	if (want)
 	{
 		*n_overlaps = ov.size() / 2;

@@ -257,7 +257,7 @@ def paths_from_genotypes(gt, alt_offsets, edges_by_alt, h_pad: int, e_pad: int, 
     rp = np.ascontiguousarray(record_ref_pos, dtype=np.uint64) if want else None
     tp = np.ascontiguousarray(edge_target_pos, dtype=np.uint64) if want else None
     n_edges = int(tp.size) if want else 0
-    cap = 1024
+    cap = max(1024, int(R))          # more overlaps than records is unusual; the call reports the needed count if it happens
     while True:
         ov = np.zeros(2 * cap, np.uint64)
         n = C.c_uint64(0)
