@@ -29,7 +29,9 @@
 // Roofline: like K3 this is a latency chain of E / P column steps plus one list extraction per candidate, not an
 // HBM-bound kernel; it reads the edge-major path matrix twice (pass A and pass C).
 #include <chrono>
+#include <cstdio>
 #include <limits>
+#include <memory>
 
 #include "pbwt_sweep.cuh"
 
@@ -198,6 +200,26 @@ k4_lists_kernel(k4_params const P)
 	if (j + 1 == P.k.n_chunks && c1 < P.n_cand && 0 != c1) k4_candidate<KW>(P, s, bins, c1);
 }
 
+
+// The lists are short (the recurrence stops at eq >= score) while their slots are cap wide: pack them before they cross
+// the host link. One warp per candidate; offsets = exclusive sum of list_n (host).
+__global__ void __launch_bounds__(256)
+k4_pack_lists_kernel(u32 const *__restrict__ list_q, u32 const *__restrict__ list_eq, u32 const *__restrict__ list_n,
+	u64 const *__restrict__ offsets, u32 const cap, u32 const n_cand, u32 *__restrict__ out_q, unsigned short *__restrict__ out_eq)
+{
+	u32 const lane(threadIdx.x & 31), n_warps(gridDim.x * (blockDim.x >> 5));
+	for (u32 c(blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)); c < n_cand; c += n_warps)
+	{
+		u32 const n(list_n[c]);
+		u64 const src(u64(c) * cap), dst(offsets[c]);
+		for (u32 i(lane); i < n; i += 32)
+		{
+			out_q[dst + i] = list_q[src + i];
+			out_eq[dst + i] = (unsigned short) list_eq[src + i];		// eq < cap <= H + 1 <= 8193
+		}
+	}
+}
+
 } // namespace v2m
 
 
@@ -234,7 +256,7 @@ namespace {
 	constexpr u32 CUT_POSITION_SCORE_MAX = std::numeric_limits<u32>::max();	// find_cut_positions.hh:17
 
 	// find_cut_positions.cc:30-42
-	struct cut_position { u64 edge{}; u64 prev_edge{EDGE_MAX}; u64 node{}; u32 score{}; };
+	struct cut_position { u64 edge{}; u64 prev_edge{EDGE_MAX}; u64 node{}; u32 score{}; u32 prev_index{}; };		// prev_index: where prev_edge was found
 }
 
 struct k4_timing { float ms_local{}, ms_compose{}, ms_lists{}, ms_host{}; u64 n_chunks{}, n_candidates{}, n_edges{}, list_entries{}, cap{}, attempts{}; };
@@ -253,6 +275,14 @@ int find_cut_positions_host(graph_holder const &gh, u64 const min_distance, std:
 	u32 const Hp(KW * K3_WARPS * 32);
 	if (g.E >= 0xfffffff0u) return fail(V2M_ERR_ARGUMENT, "find_cut_positions: edge indices do not fit 32 bits");
 	auto const t_begin(std::chrono::steady_clock::now());
+	bool const trace(nullptr != std::getenv("V2M_TRACE"));		// host-side phase times on stderr
+	auto mark([&, t_last = t_begin](char const *what) mutable {
+		if (!trace) return;
+		cudaDeviceSynchronize();
+		auto const now(std::chrono::steady_clock::now());
+		std::fprintf(stderr, "[find_cut_positions] %-28s %8.2f ms\n", what, std::chrono::duration<double, std::milli>(now - t_last).count());
+		t_last = now;
+	});
 
 	// Candidates (find_cut_positions.cc:126-132, 170-176): a function of the graph alone.
 	std::vector<cut_position> cuts;
@@ -271,6 +301,7 @@ int find_cut_positions_host(graph_holder const &gh, u64 const min_distance, std:
 		}
 	}
 	u64 const n_cand(cuts.size() - 1);
+	mark("candidates");
 	k4_timing timing{};
 	timing.n_candidates = n_cand; timing.n_edges = g.E;
 
@@ -313,6 +344,7 @@ int find_cut_positions_host(graph_holder const &gh, u64 const min_distance, std:
 		V2M_CUDA_TRY(cudaMemcpy(d_chunk_cut.p, chunk_cut.data(), chunk_cut.size() * 4, cudaMemcpyHostToDevice));
 		V2M_CUDA_TRY(cudaMemcpy(d_cut_edges.p, cut_edges.data(), n_cuts * 4, cudaMemcpyHostToDevice));
 		V2M_CUDA_TRY(cudaMemcpy(d_mtab.p, mtab.data(), mtab.size() * 4, cudaMemcpyHostToDevice));
+		mark("tables, chunks, uploads");
 
 		k4_params kp{};
 		kp.k.paths_eh = g.paths_eh; kp.k.Wh = u32(g.Wh); kp.k.H = g.H; kp.k.Hp = Hp; kp.k.n_chunks = n_chunks;
@@ -331,9 +363,14 @@ int find_cut_positions_host(graph_holder const &gh, u64 const min_distance, std:
 		cudaEventRecord(ev[1], nullptr);
 		if (int const st = k4_dispatch(KW, 1, kp, 1, smem, nullptr)) return st;
 		cudaEventRecord(ev[2], nullptr);
+		mark("passes A, B");
 
-		std::vector<u32> list_q, list_eq, list_n(n_cand);
+		std::vector<u32> list_n(n_cand);
+		std::vector<u64> list_off(n_cand + 1);
+		std::unique_ptr<u32[]> list_q;
+		std::unique_ptr<unsigned short[]> list_eq;
 		std::vector<u8> list_complete(n_cand);
+		dev_buf d_off, d_pq, d_peq;
 		u32 cap(std::min<u32>(g.H + 1, 64));
 		if (char const *env = std::getenv("V2M_K4_CAP"))			// tests force tiny caps to exercise the retry
 			if (int const v = std::atoi(env); v > 0) cap = std::min<u32>(g.H + 1, u32(v));
@@ -347,11 +384,21 @@ int find_cut_positions_host(graph_holder const &gh, u64 const min_distance, std:
 			cudaEventRecord(ev[2], nullptr);
 			if (int const st = k4_dispatch(KW, 2, kp, n_chunks, smem, nullptr)) return st;
 			cudaEventRecord(ev[3], nullptr);
-			list_q.resize(n_cand * cap); list_eq.resize(n_cand * cap);
+			mark("lists");
 			V2M_CUDA_TRY(cudaMemcpy(list_n.data(), d_n.p, n_cand * 4, cudaMemcpyDeviceToHost));
 			V2M_CUDA_TRY(cudaMemcpy(list_complete.data(), d_complete.p, n_cand, cudaMemcpyDeviceToHost));
-			V2M_CUDA_TRY(cudaMemcpy(list_q.data(), d_q.p, n_cand * cap * 4, cudaMemcpyDeviceToHost));
-			V2M_CUDA_TRY(cudaMemcpy(list_eq.data(), d_eq.p, n_cand * cap * 4, cudaMemcpyDeviceToHost));
+			list_off[0] = 0;
+			for (u64 c(0); c < n_cand; ++c) list_off[c + 1] = list_off[c] + list_n[c];
+			u64 const n_pairs(list_off[n_cand]);
+			if (d_off.alloc((n_cand + 1) * 8) || d_pq.alloc(std::max<u64>(1, n_pairs) * 4) || d_peq.alloc(std::max<u64>(1, n_pairs) * 2)) return V2M_ERR_CUDA;
+			V2M_CUDA_TRY(cudaMemcpy(d_off.p, list_off.data(), (n_cand + 1) * 8, cudaMemcpyHostToDevice));
+			k4_pack_lists_kernel<<<u32(sms) * 8, 256>>>(d_q.as<u32>(), d_eq.as<u32>(), d_n.as<u32>(), d_off.as<u64>(), cap, u32(n_cand), d_pq.as<u32>(), d_peq.as<unsigned short>());
+			V2M_CHECK_LAUNCH("k4_pack_lists_kernel");
+			list_q.reset(new u32[std::max<u64>(1, n_pairs)]);				// not value-initialised: the copies fill them
+			list_eq.reset(new unsigned short[std::max<u64>(1, n_pairs)]);
+			V2M_CUDA_TRY(cudaMemcpy(list_q.get(), d_pq.p, n_pairs * 4, cudaMemcpyDeviceToHost));
+			V2M_CUDA_TRY(cudaMemcpy(list_eq.get(), d_peq.p, n_pairs * 2, cudaMemcpyDeviceToHost));
+			mark("pack + copy lists");
 
 			// The recurrence (find_cut_positions.cc:131-166) over the lists.
 			bool need_more(false);
@@ -361,7 +408,8 @@ int find_cut_positions_host(graph_holder const &gh, u64 const min_distance, std:
 				cut_position &cur(cuts[c + 1]);
 				cur.score = g.H; cur.prev_edge = EDGE_MAX;
 				u32 const n(list_n[c]);
-				u32 const *lq(list_q.data() + c * cap), *le(list_eq.data() + c * cap);
+				u32 const *lq(list_q.get() + list_off[c]);
+				unsigned short const *le(list_eq.get() + list_off[c]);
 				entries += n;
 				bool stopped(false);
 				for (u32 i(0); i < n; ++i)
@@ -372,13 +420,14 @@ int find_cut_positions_host(graph_holder const &gh, u64 const min_distance, std:
 					if (min_distance <= gh.alnpos[cur.node] - gh.alnpos[prev.node])
 					{
 						u32 const cand(std::max(eq, prev.score));			// cut_position::update_if_needed, :57-65
-						if (cand < cur.score) { cur.score = cand; cur.prev_edge = prev.edge; }
+						if (cand < cur.score) { cur.score = cand; cur.prev_edge = prev.edge; cur.prev_index = lq[i]; }
 					}
 				}
 				// Pairs left out have eq >= cap: harmless iff the score is already at most cap.
 				if (!stopped && !list_complete[c] && cur.score > cap) { need_more = true; break; }
 			}
 			timing.list_entries = entries; timing.cap = cap;
+			mark("recurrence");
 			if (!need_more) break;
 			if (cap > g.H) return fail(V2M_ERR_STATE, "find_cut_positions: incomplete candidate list at full capacity");
 			cap = (cap < 512 && g.H + 1 > 512) ? 512 : g.H + 1;
@@ -397,15 +446,14 @@ int find_cut_positions_host(graph_holder const &gh, u64 const min_distance, std:
 		for (;;)
 		{
 			out_cut_positions.push_back(cuts[it].node);
-			u64 const prev_edge(cuts[it].prev_edge);
-			if (EDGE_MAX == prev_edge) break;
-			it = std::size_t(std::lower_bound(cuts.begin(), cuts.begin() + it, prev_edge,
-				[](cut_position const &cp, u64 const e) { return cp.edge < e; }) - cuts.begin());
+			if (EDGE_MAX == cuts[it].prev_edge) break;
+			it = cuts[it].prev_index;		// the reference finds prev_edge by lower_bound (:190-196); the entries M() reaches have distinct edges, so this is that entry
 		}
 		if (0 != out_cut_positions.back()) out_cut_positions.push_back(0);
 		std::reverse(out_cut_positions.begin(), out_cut_positions.end());
 		if (out_cut_positions.back() != g.N - 1) out_cut_positions.back() = g.N - 1;
 	}
+	mark("trace-back");
 	timing.ms_host = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t_begin).count();
 	last_k4_timing() = timing;
 	return V2M_OK;

@@ -5,6 +5,9 @@
 // it is kept as host C++ by design. The reference's std::multimap<class, founder> holds at most founder_count entries and is
 // rebuilt at every cut (27 M node allocations on c3); it is replaced by a sorted vector with the same observable behaviour.
 #include <algorithm>
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
 #include <utility>
 #include <vector>
 
@@ -27,28 +30,62 @@ namespace {
 		bool operator<(joined_class const &other) const { return size < other.size; }
 	};
 
-	// std::multimap<u32, u32> as the reference uses it (founder_…cc:174, 283, 340-360, 441-447), on a sorted vector:
-	// insert places the pair after the pairs with an equal key (libstdc++ _M_get_insert_equal_pos descends to the right on
-	// equality), find returns the first pair with the key (lower bound), begin is the first pair of the smallest key.
-	class flat_multimap
+	// std::multimap<u32, u32> (class representative → founder) as the reference uses it (founder_…cc:174, 283, 340-360,
+	// 441-447), without a tree: the keys are chromosome copy indices, so every key owns a FIFO of founders threaded through
+	// m_next and found by direct indexing. What the reference's container guarantees and the matching depends on:
+	// insert places a pair after the pairs with an equal key (libstdc++ _M_get_insert_equal_pos descends to the right on
+	// equality) → FIFO per key; find returns the first pair with the key → the FIFO's head; begin is the first pair of the
+	// smallest key → the head of the smallest key with a non-empty FIFO (keys sorted on first use, then a cursor that only
+	// moves forward, since between two rebuilds pairs are only removed).
+	class founders_by_class
 	{
-		std::vector<std::pair<u32, u32>>	m_items;
+		static constexpr u32 NONE = 0xffffffffu;
+		std::vector<u32>	m_stamp, m_head, m_tail;		// by key
+		std::vector<u32>	m_next;							// by founder
+		std::vector<u32>	m_keys;							// distinct keys of this epoch
+		u32					m_epoch{1}, m_count{0}, m_cursor{0};
+		bool				m_sorted{false};
+		// A founder that has not been given a class yet is filed under PLOIDY_MAX (:170-172, 441-447), the greatest key:
+		// it gets the slot after the last chromosome copy.
+		u32 index_of(u32 const key) const { return std::min<u32>(key, u32(m_stamp.size() - 1)); }
 	public:
-		typedef std::vector<std::pair<u32, u32>>::iterator iterator;
-		iterator begin() { return m_items.begin(); }
-		iterator end() { return m_items.end(); }
-		bool empty() const { return m_items.empty(); }
-		void clear() { m_items.clear(); }
-		void erase(iterator it) { m_items.erase(it); }
-		void emplace(u32 const key, u32 const value)
+		founders_by_class(u32 const n_copies, u32 const n_founders): m_stamp(n_copies + 1, 0), m_head(n_copies + 1), m_tail(n_copies + 1), m_next(n_founders, NONE) {}
+		bool empty() const { return 0 == m_count; }
+		void clear()
 		{
-			auto const it(std::upper_bound(m_items.begin(), m_items.end(), key, [](u32 const k, std::pair<u32, u32> const &p) { return k < p.first; }));
-			m_items.insert(it, {key, value});
+			if (0 == ++m_epoch) { std::fill(m_stamp.begin(), m_stamp.end(), 0); m_epoch = 1; }
+			m_keys.clear(); m_count = 0; m_cursor = 0; m_sorted = false;
 		}
-		iterator find(u32 const key)
+		void emplace(u32 const class_key, u32 const founder)
 		{
-			auto const it(std::lower_bound(m_items.begin(), m_items.end(), key, [](std::pair<u32, u32> const &p, u32 const k) { return p.first < k; }));
-			return (it != m_items.end() && it->first == key) ? it : m_items.end();
+			u32 const key(index_of(class_key));
+			m_next[founder] = NONE;
+			if (m_stamp[key] != m_epoch)
+			{
+				m_stamp[key] = m_epoch; m_head[key] = founder; m_tail[key] = founder;
+				m_keys.push_back(key); m_sorted = false; m_cursor = 0;
+			}
+			else if (NONE == m_head[key]) { m_head[key] = founder; m_tail[key] = founder; }
+			else { m_next[m_tail[key]] = founder; m_tail[key] = founder; }
+			++m_count;
+		}
+		// find(key) + erase: the first founder filed under key.
+		bool pop(u32 const class_key, u32 &founder)
+		{
+			u32 const key(index_of(class_key));
+			if (m_stamp[key] != m_epoch || NONE == m_head[key]) return false;
+			founder = m_head[key];
+			m_head[key] = m_next[founder];
+			--m_count;
+			return true;
+		}
+		// begin() + erase.
+		bool pop_first(u32 &founder)
+		{
+			if (0 == m_count) return false;
+			if (!m_sorted) { std::sort(m_keys.begin(), m_keys.end()); m_sorted = true; m_cursor = 0; }
+			while (NONE == m_head[m_keys[m_cursor]]) ++m_cursor;
+			return pop(m_keys[m_cursor], founder);
 		}
 	};
 
@@ -71,15 +108,41 @@ namespace {
 		u32							m_founders;
 		u64							m_segments;
 		u32							*m_assigned;			// column-major: (segment, founder) → m_assigned[founder * segments + segment]
-		flat_multimap				m_by_class;				// class representative on the current lhs → founder
+		founders_by_class			m_by_class;				// class representative on the current lhs → founder
 		stamp_set					m_reserved;				// by chromosome copy
 		std::vector<u32>			m_arbitrary_rhs;
 
-		u32 &slot(u64 const segment, u32 const founder) { return m_assigned[u64(founder) * m_segments + segment]; }
+		// The row of the segment being matched is kept here and leaves for m_assigned in blocks of BLOCK segments, so that the
+		// column-major matrix is written in runs instead of one word per founder per cut.
+		static constexpr u64		BLOCK = 512;
+		std::vector<u32>			m_row;					// [founder]
+		std::vector<u32>			m_block;				// [segment - m_block_first][founder]
+		u64							m_block_first{0}, m_block_fill{0};
+
+		void flush_block()
+		{
+			for (u32 f(0); f < m_founders; ++f)
+			{
+				u32 *dst(m_assigned + u64(f) * m_segments + m_block_first);
+				for (u64 i(0); i < m_block_fill; ++i) dst[i] = m_block[i * m_founders + f];
+			}
+			m_block_first += m_block_fill;
+			m_block_fill = 0;
+		}
+
+		// Segments are finished in order, each exactly once.
+		void finish_row()
+		{
+			std::copy(m_row.begin(), m_row.end(), m_block.begin() + m_block_fill * m_founders);
+			if (BLOCK == ++m_block_fill) flush_block();
+		}
 
 	public:
 		founder_matcher(u32 copies, u32 founders, u64 segments, u32 *assigned):
-			m_founders(founders), m_segments(segments), m_assigned(assigned), m_reserved(copies) {}
+			m_founders(founders), m_segments(segments), m_assigned(assigned), m_by_class(copies, founders), m_reserved(copies),
+			m_row(founders, V2M_PLOIDY_MAX), m_block(BLOCK * founders) {}
+
+		void finish() { flush_block(); }
 
 		// :268-320 — founders of the first segment, largest joined classes first; every lhs class gets one founder
 		// before any class gets a second one.
@@ -91,7 +154,7 @@ namespace {
 			u32 next_founder(0);
 			auto const place([&](joined_class const &jc) {
 				m_by_class.emplace(jc.lhs, next_founder);
-				slot(0, next_founder) = jc.lhs;
+				m_row[next_founder] = jc.lhs;
 				++next_founder;
 			});
 			for (auto it(by_size.rbegin()); it != by_size.rend(); ++it)
@@ -116,6 +179,7 @@ namespace {
 					--free_founders;
 					place(*it);
 				}
+			finish_row();
 			return V2M_OK;
 		}
 
@@ -124,24 +188,21 @@ namespace {
 		{
 			m_reserved.clear();
 			m_arbitrary_rhs.clear();
+			std::fill(m_row.begin(), m_row.end(), V2M_PLOIDY_MAX);		// :170-172
 			u32 free_founders(m_founders);
 			u32 to_reserve(std::min(free_founders, rhs_distinct));
 			free_founders -= to_reserve;
 
 			auto const follow([&](joined_class const &jc) -> bool {			// :340-352
-				auto const it(m_by_class.find(jc.lhs));
-				if (m_by_class.end() == it) return false;
-				u32 const founder(it->second);
-				m_by_class.erase(it);
-				slot(segment, founder) = jc.rhs;
+				u32 founder;
+				if (!m_by_class.pop(jc.lhs, founder)) return false;
+				m_row[founder] = jc.rhs;
 				return true;
 			});
 			auto const take_any([&](u32 const rhs) -> bool {					// :354-360
-				if (m_by_class.empty()) return false;
-				auto const it(m_by_class.begin());
-				u32 const founder(it->second);
-				m_by_class.erase(it);
-				slot(segment, founder) = rhs;
+				u32 founder;
+				if (!m_by_class.pop_first(founder)) return false;
+				m_row[founder] = rhs;
 				return true;
 			});
 
@@ -191,7 +252,8 @@ namespace {
 			// :441-447
 			m_by_class.clear();
 			for (u32 f(0); f < m_founders; ++f)
-				m_by_class.emplace(slot(segment, f), f);
+				m_by_class.emplace(m_row[f], f);
+			finish_row();
 			return V2M_OK;
 		}
 	};
@@ -211,10 +273,19 @@ extern "C" int v2m_cuda_find_matchings(v2m_graph_t g, const uint64_t *cut_positi
 	u64 const segments(n_cuts - 1);
 	std::fill(assigned, assigned + segments * founder_count, V2M_PLOIDY_MAX);		// :170-172
 
+	bool const trace(nullptr != std::getenv("V2M_TRACE"));		// host-side phase times on stderr
+	auto t_last(std::chrono::steady_clock::now());
+	auto mark([&](char const *what) {
+		if (!trace) return;
+		auto const now(std::chrono::steady_clock::now());
+		std::fprintf(stderr, "[find_matchings] %-28s %8.2f ms\n", what, std::chrono::duration<double, std::milli>(now - t_last).count());
+		t_last = now;
+	});
 	std::vector<u32> rhs_eq, distinct, first_class, joined;
 	std::vector<u8> first_is_ref;
 	std::vector<u64> offsets;
 	if (int const st = segment_classes_host(*g, cut_positions, n_cuts, false, 0, rhs_eq, distinct, first_class, first_is_ref, offsets, joined)) return st;
+	mark("segment classes (K3 + copies)");
 
 	std::vector<joined_class> by_size;
 	auto const classes_of_cut([&](u64 const c) {		// cut index c >= 1 → its joined classes, in permutation order
@@ -249,6 +320,8 @@ extern "C" int v2m_cuda_find_matchings(v2m_graph_t g, const uint64_t *cut_positi
 			if (int const st = matcher.seed_first_segment(by_size, distinct[0])) return st;
 		if (int const st = matcher.extend(c - 1, by_size, distinct[c - 1])) return st;
 	}
+	matcher.finish();
+	mark("greedy assignment");
 	*found = 1;
 	return V2M_OK;
 }
