@@ -64,6 +64,36 @@ __global__ void __launch_bounds__(256) fill_tiles_bulk(u8 *dst, u64 pitch, u32 r
 	if (0 == lane) bulk_wait_read<0>();
 }
 
+// generalised: WARPS warps per CTA; SPLIT > 1: the CTA covers SPLIT adjacent tiles, warp groups take one each, so that
+// neighbouring pieces of a row are written at about the same time
+template <int TCOL, int BUFS, int ROWS, int WARPS, int SPLIT>
+__global__ void __launch_bounds__(WARPS * 32) fill_tiles_gen(u8 *dst, u64 pitch, u32 rows)
+{
+	extern __shared__ __align__(128) u8 sm[];
+	unsigned const lane(threadIdx.x & 31), warp(threadIdx.x >> 5);
+	constexpr int GW = WARPS / SPLIT;						// warps per tile
+	u64 const t0((u64(blockIdx.x) * SPLIT + warp / GW) * TCOL);
+	u32 const rb0(blockIdx.y * ROWS);
+	uint4 v[TCOL / 512];
+	for (int j = 0; j < TCOL / 512; ++j) v[j] = make_uint4(0x41414141u + j, 0x43434343u, 0x47474747u, 0x54545454u + lane);
+	u8 *mine(sm + warp * BUFS * TCOL);
+	int k(0);
+	for (u32 r(rb0 + warp % GW); r < min(rb0 + ROWS, rows); r += GW, ++k)
+	{
+		u8 *buf(mine + (k % BUFS) * TCOL);
+		if (k >= BUFS) { if (0 == lane) bulk_wait_read<BUFS - 1>(); __syncwarp(); }
+#pragma unroll
+		for (int j = 0; j < TCOL / 512; ++j) *reinterpret_cast<uint4 *>(buf + j * 512 + lane * 16) = v[j];
+		fence_proxy_async_smem();
+		__syncwarp();
+		if (0 == lane) { bulk_s2g(dst + u64(r) * pitch + t0, buf, TCOL); bulk_commit(); }
+	}
+	if (0 == lane) bulk_wait_read<0>();
+}
+
+template <int TCOL, int BUFS, int ROWS, int WARPS, int SPLIT>
+static void run_gen(u8 *d, u64 pitch, u32 rows, u64 A);
+
 template <typename F>
 static void timeit(char const *name, double bytes, F &&launch)
 {
@@ -78,6 +108,18 @@ static void timeit(char const *name, double bytes, F &&launch)
 	CK(cudaGetLastError());
 	float ms; CK(cudaEventElapsedTime(&ms, e0, e1));
 	printf("%-44s %8.3f ms  %8.1f GB/s\n", name, ms / iters, bytes / (ms / iters * 1e-3) / 1e9);
+}
+
+template <int TCOL, int BUFS, int ROWS, int WARPS, int SPLIT>
+static void run_gen(u8 *d, u64 pitch, u32 rows, u64 A)
+{
+	auto k(fill_tiles_gen<TCOL, BUFS, ROWS, WARPS, SPLIT>);
+	int const smem(WARPS * BUFS * TCOL);
+	CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+	int occ(0); CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k, WARPS * 32, smem));
+	u64 const n_ctas_x(A / (u64(TCOL) * SPLIT));
+	char nm[96]; snprintf(nm, 96, "gen<%d,bufs %d,rows %d,warps %d,split %d> occ %d", TCOL, BUFS, ROWS, WARPS, SPLIT, occ);
+	timeit(nm, double(n_ctas_x) * TCOL * SPLIT * rows, [&]{ k<<<dim3(unsigned(n_ctas_x), (rows + ROWS - 1) / ROWS), WARPS * 32, smem>>>(d, pitch, rows); });
 }
 
 int main()
@@ -112,6 +154,21 @@ int main()
 		auto k5(fill_tiles_bulk<4096, 4, 64>); CK(cudaFuncSetAttribute(k5, cudaFuncAttributeMaxDynamicSharedMemorySize, 8 * 4 * 4096));
 		timeit("fill_tiles_bulk<4096,4,64> restage=1", double(n_tiles4k) * 4096 * rows, [&]{ k5<<<dim3(n_tiles4k, rows / 64), 256, 8 * 4 * 4096>>>(d, pitch, rows, 1); });
 	}
+	run_gen<4096, 2, 64, 8, 1>(d, pitch, rows, A);
+	run_gen<4096, 2, 64, 8, 2>(d, pitch, rows, A);
+	run_gen<4096, 2, 32, 8, 2>(d, pitch, rows, A);
+	run_gen<4096, 2, 128, 8, 2>(d, pitch, rows, A);
+	run_gen<4096, 2, 64, 8, 4>(d, pitch, rows, A);
+	run_gen<8192, 2, 64, 4, 1>(d, pitch, rows, A);
+	run_gen<8192, 2, 32, 4, 1>(d, pitch, rows, A);
+	run_gen<8192, 2, 128, 4, 1>(d, pitch, rows, A);
+	run_gen<8192, 2, 64, 8, 1>(d, pitch, rows, A);
+	run_gen<8192, 2, 128, 8, 1>(d, pitch, rows, A);
+	run_gen<8192, 3, 64, 4, 1>(d, pitch, rows, A);
+	run_gen<16384, 2, 64, 4, 1>(d, pitch, rows, A);
+	run_gen<16384, 2, 64, 2, 1>(d, pitch, rows, A);
+	run_gen<16384, 2, 128, 2, 1>(d, pitch, rows, A);
+	run_gen<8192, 2, 64, 2, 1>(d, pitch, rows, A);
 	// copy for reference (read + write bytes)
 	{
 		u8 *s; CK(cudaMalloc(&s, bytes / 2));

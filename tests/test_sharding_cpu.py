@@ -90,7 +90,13 @@ def _free_port():
 @pytest.mark.parametrize("unaligned,omit_ref", [(False, False), (True, False), (False, True)])
 def test_two_rank_gloo_stream(tmp_path, unaligned, omit_ref):
     import torch.multiprocessing as mp
-    mp.spawn(_worker, args=(2, _free_port(), str(tmp_path), unaligned, omit_ref), nprocs=2, join=True)
+    for attempt in range(3):        # the probed port can be taken by someone else before the ranks bind it
+        try:
+            mp.spawn(_worker, args=(2, _free_port(), str(tmp_path), unaligned, omit_ref), nprocs=2, join=True)
+            break
+        except Exception as exc:
+            if attempt == 2 or "address" not in str(exc).lower():
+                raise
 
 
 def test_single_process_stream(tmp_path):

@@ -5,7 +5,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libv2m_cuda.so")
+# V2M_CUDA_LIB: another build of the same library (kernel experiments); it must exist all the same.
+LIB_PATH = os.environ.get("V2M_CUDA_LIB") or os.path.join(_HERE, "libv2m_cuda.so")
 
 PLOIDY_MAX = 0xFFFFFFFF
 

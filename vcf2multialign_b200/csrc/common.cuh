@@ -61,6 +61,11 @@ __device__ __forceinline__ void mbar_expect_tx(u64 *bar, u32 const bytes)
 	asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(smem_u32(bar)), "r"(bytes) : "memory");
 }
 
+__device__ __forceinline__ void mbar_arrive(u64 *bar)
+{
+	asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(smem_u32(bar)) : "memory");
+}
+
 __device__ __forceinline__ void mbar_wait(u64 *bar, u32 const parity)
 {
 	asm volatile(

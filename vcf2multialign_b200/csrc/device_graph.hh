@@ -27,7 +27,10 @@ namespace v2m {
 
 constexpr int K2_TCOL = 4096;			// columns per emit_rows tile
 constexpr int K2_THREADS = 256;
-constexpr int K2_ROWS_PER_CTA = 64;
+#ifndef V2M_K2_ROWS_PER_CTA
+#define V2M_K2_ROWS_PER_CTA 64
+#endif
+constexpr int K2_ROWS_PER_CTA = V2M_K2_ROWS_PER_CTA;
 
 struct device_graph
 {

@@ -15,9 +15,17 @@
 //   compose_founder_kernel  path bits of founder rows: per segment the bits of the assigned chromosome copy
 //                           (founder_sequence_writing_delegate::handle_node, founder_…cc:106-114).
 //   resolve_rows_kernel     K2a: path bits → taken bits, one warp per row, 2048 edges per step.
-//   emit_rows_kernel        K2b: rows × columns tile writer; template tile + edge records staged in shared memory by
-//                           bulk async copies, rows assembled in shared memory and written by the TMA engine.
+//   emit_rows_kernel        K2b: rows × columns tile writer, persistent CTAs; template tile + edge records staged in shared
+//                           memory by bulk async copies one tile ahead, rows assembled in shared memory and written by
+//                           the TMA engine.
 //                           Algorithmic bytes: rows × columns written. Roofline: HBM write.
+#include <algorithm>
+#include <cstdlib>
+#include <map>
+#include <mutex>
+#include <thread>
+#include <tuple>
+
 #include "common.cuh"
 #include "device_graph.hh"
 
@@ -198,31 +206,63 @@ resolve_rows_kernel(u64 const * __restrict__ lines, u32 const * __restrict__ lin
 // ---------------------------------------------------------------------------------------------------------
 // K2b emit_rows
 // ---------------------------------------------------------------------------------------------------------
-// One CTA = one tile of K2_TCOL aligned columns × K2_ROWS_PER_CTA rows.
-//   stage   one thread issues three bulk async copies (TMA engine) global → shared: the tile of the REF template, the
-//           records of the ALT edges that can intersect the tile and those edges' label bytes (contiguous in the
-//           flattened label store), so that patching never leaves the SM;
-//   rows    each warp owns K2_ROWS_PER_CTA / 8 rows and two K2_TCOL-byte row buffers in shared memory. Per row: the
-//           template tile (kept in registers) is written to a buffer with 128-bit STS, the row's taken edges that
-//           touch the tile are patched in (label bytes + '-'), and one lane hands the finished buffer to the TMA
-//           engine (cp.async.bulk shared → global): the LSU issues no global stores at all, and HBM only ever sees
-//           whole 128-byte lines. The taken-edge words of all rows of a warp are fetched up front (independent loads
-//           in flight), so no row waits on a dependent global load chain.
+// Persistent CTAs, one per SM: K2P_CWARPS row-writing warps and one staging warp.
+//   units   the launch is cut into units of one tile of K2_TCOL aligned columns × rows_per_unit (<= K2P_UNIT_ROWS) rows,
+//           numbered tile-fastest. CTAs draw unit numbers from a ticket counter, so an SM that is served more slowly by
+//           the memory system simply takes fewer units (with a fixed assignment single SMs ran 20 % longer than the
+//           rest); the last CTA to find the counter exhausted zeroes it for the next launch on the stream.
+//   stage   per unit the staging warp (a) has one lane issue three bulk async copies (TMA engine) global → shared: the
+//           tile of the REF template, the records of the ALT edges that can intersect the tile and those edges' label
+//           bytes (contiguous in the flattened label store), so that patching never leaves the SM; (b) gathers the
+//           rows' taken-edge words that cover the tile's edges into shared memory. K2P_STAGES stage buffers with full /
+//           empty mbarriers: the next unit is staged while the rows of the current one are written, so the row warps
+//           never issue a global load and never wait for a tile (with one tile per CTA and no prefetch all CTAs of a
+//           wave waited together: 15 % of the kernel; reads queued behind the write stream take microseconds).
+//   rows    the (unit, row) items of a CTA are dealt to its row warps round-robin across unit boundaries, so every warp
+//           writes the same number of rows. Each warp owns two K2_TCOL-byte row buffers in shared memory. Per row: the
+//           template tile (kept in registers while the warp stays in a unit) is written to a buffer with 128-bit STS,
+//           the row's taken edges that touch the tile are patched in (label bytes + '-'), and one lane hands the
+//           finished buffer to the TMA engine (cp.async.bulk shared → global): the LSU issues no global stores at all,
+//           and HBM only ever sees whole 128-byte lines.
 // Algorithmic bytes: rows × columns written (+ < 1 % reads). Roofline: HBM write.
 constexpr int K2_EDGE_CAP = 256;								// ALT edge records staged per tile (c2 averages ~100)
 constexpr int K2_LABEL_CAP = 2048;								// label bytes staged per tile (incl. ≤ 15 bytes of alignment slack)
-constexpr int K2_WARPS = K2_THREADS / 32;
+#ifndef V2M_K2P_CWARPS
+#define V2M_K2P_CWARPS 19
+#endif
+constexpr int K2P_CWARPS = V2M_K2P_CWARPS;						// row warps per CTA: 20 warps in all leave 96 registers per thread (24 would spill)
+constexpr int K2P_THREADS = (K2P_CWARPS + 1) * 32;				// + the staging warp
+#ifndef V2M_K2P_STAGES
+#define V2M_K2P_STAGES 2
+#endif
+constexpr int K2P_STAGES = V2M_K2P_STAGES;						// stage buffers: the staging warp runs up to K2P_STAGES - 1 units ahead
+constexpr u32 K2P_DONE = 0xffffffffu;								// header word 3: no unit left
 constexpr int K2_CHUNKS = K2_TCOL / 512;						// 16-byte chunks of the tile per lane
 constexpr u32 K2_SHORT_PATCH = 16;								// longer spans are written by the whole warp
 
-struct emit_smem
+#ifndef V2M_K2P_UNIT_ROWS
+#define V2M_K2P_UNIT_ROWS 64
+#endif
+constexpr int K2P_UNIT_ROWS = V2M_K2P_UNIT_ROWS;				// rows per unit at most
+constexpr int K2P_WORDS = 4;									// taken-edge words staged per row (a tile of c2 spans 2 – 3)
+
+struct emit_stage
 {
 	alignas(128) u8			tmpl[K2_TCOL];
 	alignas(128) edge_rec	edges[K2_EDGE_CAP];
 	alignas(128) u8			labels[K2_LABEL_CAP];
-	alignas(128) u8			rows[K2_WARPS][2][K2_TCOL];
-	alignas(8) u64			bar;
+	alignas(128) u64		words[K2P_UNIT_ROWS][K2P_WORDS];	// the rows' taken-edge words that cover the tile's edges
 };
+
+struct emit_smem
+{
+	emit_stage				stage[K2P_STAGES];
+	alignas(128) u8			rows[K2P_CWARPS][2][K2_TCOL];
+	alignas(16) uint4		hdr[K2P_STAGES];	// per stage: tile_edges.x, tile_edges.y, label window base, unit << 2 | words staged? << 1 | edges staged? (K2P_DONE: none)
+	alignas(8) u64			full[K2P_STAGES];	// the stage's copies have landed (transaction bytes)
+	alignas(8) u64			empty[K2P_STAGES];	// every row warp is done with the stage
+};
+static_assert(sizeof(emit_smem) <= 227 * 1024);
 
 struct emit_params
 {
@@ -236,6 +276,9 @@ struct emit_params
 	u32				row_begin, row_end;
 	u64				col_begin, col_end;	// col_begin % 16 == 0
 	u64				first_tile;			// col_begin / K2_TCOL
+	u32				n_tiles;			// tiles the column window touches
+	u32				rows_per_unit, n_row_chunks;
+	u32				*tickets;			// [0] next unit, [1] CTAs that ran out of units; both 0 between launches
 	u8				*out;
 	u64				pitch;
 };
@@ -247,153 +290,244 @@ __device__ __forceinline__ u8 patch_byte(edge_rec const &rec, u8 const *labels, 
 	return k < rec.label_len ? labels[rec.label_off + k] : u8('-');
 }
 
-__global__ void __launch_bounds__(K2_THREADS, 3)
+__global__ void __launch_bounds__(K2P_THREADS, 1)
 emit_rows_kernel(emit_params const p)
 {
 	extern __shared__ __align__(128) u8 smem_raw[];
 	emit_smem &sm(*reinterpret_cast<emit_smem *>(smem_raw));
 
 	unsigned const lane(threadIdx.x & 31), warp(threadIdx.x >> 5);
-	u64 const tile(p.first_tile + blockIdx.x);
-	u64 const t0(tile * K2_TCOL);
-	u64 const c0(max(t0, p.col_begin)), c1(min(t0 + K2_TCOL, p.col_end));
-	u32 const rb0(p.row_begin + blockIdx.y * K2_ROWS_PER_CTA);
-	u32 const rb1(min(rb0 + K2_ROWS_PER_CTA, p.row_end));
+	u32 const n_units(p.n_tiles * p.n_row_chunks);
+	u32 const RC(p.rows_per_unit);					// <= K2P_UNIT_ROWS
 
-	uint2 const te(p.tile_edges[tile]);
-	u32 const n_e(te.y - te.x);
-	bool const has_edges(0 != n_e);
-	uint2 const tl(p.tile_labels[tile]);
-	u32 const lab_base(tl.x & ~15u);											// bulk copies start at 16-byte boundaries
-	u32 const lab_bytes(tl.y > tl.x ? ((tl.y - lab_base + 15u) & ~15u) : 0);
-	bool const staged(n_e <= K2_EDGE_CAP && lab_bytes <= K2_LABEL_CAP);
-	u64 const w_lo(te.x / 64), w_hi(has_edges ? (te.y - 1) / 64 : w_lo);
-	u32 const n_words(has_edges ? u32(w_hi - w_lo + 1) : 0);
-
-	// ---- stage the template tile and the tile's edge records ---------------------------------------------------------
 	if (0 == threadIdx.x)
 	{
-		mbar_init(&sm.bar, 1);
+		for (int i = 0; i < K2P_STAGES; ++i) { mbar_init(&sm.full[i], 2); mbar_init(&sm.empty[i], K2P_CWARPS); }
 		fence_mbar_init();
-		u32 const edge_bytes(staged ? n_e * u32(sizeof(edge_rec)) : 0);
-		u32 const label_bytes(staged ? lab_bytes : 0);
-		mbar_expect_tx(&sm.bar, K2_TCOL + edge_bytes + label_bytes);
-		bulk_g2s(sm.tmpl, p.tmpl + t0, K2_TCOL, &sm.bar);
-		if (edge_bytes) bulk_g2s(sm.edges, p.edges + te.x, edge_bytes, &sm.bar);
-		if (label_bytes) bulk_g2s(sm.labels, p.label_chars + lab_base, label_bytes, &sm.bar);
+	}
+	__syncthreads();
+
+	// ---- staging warp: template tile, edge records and labels of the units, one unit ahead of the rows ------------------
+	if (K2P_CWARPS == warp)
+	{
+		// One unit ahead of itself: the ticket and the tile's edge range of unit k + 1 are asked for while the words of unit k
+		// are on their way, so that the warp spends one memory latency per unit, not three.
+		auto const next_ticket([&]() -> u32 { return __shfl_sync(0xffffffffu, 0 == lane ? atomicAdd(p.tickets, 1u) : 0u, 0); });
+		auto const edges_of([&](u32 const u) -> uint2 { return u < n_units ? p.tile_edges[p.first_tile + u % p.n_tiles] : make_uint2(0, 0); });
+		u32 unit(next_ticket());
+		uint2 te(edges_of(unit));
+#pragma unroll 1
+		for (u32 k(0); ; ++k)
+		{
+			u32 const s(k % K2P_STAGES);
+			if (k >= K2P_STAGES) mbar_wait(&sm.empty[s], (k / K2P_STAGES - 1) & 1);		// the rows of unit k - K2P_STAGES are done with this stage
+			if (unit >= n_units)
+			{
+				if (0 == lane)
+				{
+					sm.hdr[s] = make_uint4(0, 0, 0, K2P_DONE);
+					mbar_arrive(&sm.full[s]);
+					mbar_arrive(&sm.full[s]);
+				}
+				break;
+			}
+			u32 const unit_after(next_ticket());
+			u64 const tile(p.first_tile + unit % p.n_tiles);
+			u64 const w_lo(te.x / 64);
+			u32 const n_words(te.y != te.x ? u32((te.y - 1) / 64 - w_lo + 1) : 0);
+			bool const words_staged(n_words <= K2P_WORDS);
+			if (0 == lane)
+			{
+				uint2 const tl(p.tile_labels[tile]);
+				u32 const n_e(te.y - te.x);
+				u32 const lab_base(tl.x & ~15u);										// bulk copies start at 16-byte boundaries
+				u32 const lab_bytes(tl.y > tl.x ? ((tl.y - lab_base + 15u) & ~15u) : 0);
+				bool const staged(n_e <= K2_EDGE_CAP && lab_bytes <= K2_LABEL_CAP);
+				u32 const edge_bytes(staged ? n_e * u32(sizeof(edge_rec)) : 0);
+				u32 const label_bytes(staged ? lab_bytes : 0);
+				sm.hdr[s] = make_uint4(te.x, te.y, lab_base, unit << 2 | (words_staged ? 2u : 0u) | (staged ? 1u : 0u));
+				mbar_expect_tx(&sm.full[s], K2_TCOL + edge_bytes + label_bytes);
+				bulk_g2s(sm.stage[s].tmpl, p.tmpl + tile * K2_TCOL, K2_TCOL, &sm.full[s]);
+				if (edge_bytes) bulk_g2s(sm.stage[s].edges, p.edges + te.x, edge_bytes, &sm.full[s]);
+				if (label_bytes) bulk_g2s(sm.stage[s].labels, p.label_chars + lab_base, label_bytes, &sm.full[s]);
+			}
+			// The rows' taken-edge words for this tile, gathered by the whole warp: all loads first, then the stores.
+			constexpr int PER_LANE = K2P_UNIT_ROWS * K2P_WORDS / 32;
+			u64 got[PER_LANE];
+			bool const gather(words_staged && 0 != n_words);
+			if (gather)
+			{
+				u32 const rb0(p.row_begin + (unit / p.n_tiles) * RC);
+				u32 const rb1(min(rb0 + RC, p.row_end));
+#pragma unroll
+				for (int j = 0; j < PER_LANE; ++j)
+				{
+					u32 const idx(j * 32 + lane), row(idx / K2P_WORDS), i(idx % K2P_WORDS);
+					got[j] = (rb0 + row < rb1 && i < n_words) ? p.taken[u64(rb0 + row) * p.We + w_lo + i] : 0;
+				}
+			}
+			uint2 const te_after(edges_of(unit_after));
+			if (gather)
+			{
+#pragma unroll
+				for (int j = 0; j < PER_LANE; ++j)
+				{
+					u32 const idx(j * 32 + lane);
+					sm.stage[s].words[idx / K2P_WORDS][idx % K2P_WORDS] = got[j];
+				}
+			}
+			__syncwarp();
+			if (0 == lane) mbar_arrive(&sm.full[s]);		// release: the header and the words are visible to the waiters
+			unit = unit_after;
+			te = te_after;
+		}
+		if (0 != lane) return;
+		// The last CTA to run out of units leaves the tickets as it found them, for the next launch on this stream.
+		if (atomicAdd(p.tickets + 1, 1u) == gridDim.x - 1)
+		{
+			p.tickets[0] = 0;
+			p.tickets[1] = 0;
+		}
+		return;
 	}
 
-	// Meanwhile: taken-edge words of this warp's first rows (lane ↔ word; the loop below stays two rows ahead).
-	auto const load_word([&](u32 const r, u32 const i) -> u64 {
-		if (r >= rb1 || i >= n_words) return 0;
-		u64 const w(w_lo + i);
-		u64 word(p.taken[u64(r) * p.We + w]);
-		if (w == w_lo) word &= ~u64(0) << (te.x % 64);
-		if (w == w_hi && 0 != te.y % 64) word &= (u64(1) << (te.y % 64)) - 1;
-		return word;
-	});
-	u64 w_cur(load_word(rb0 + warp, lane));
-	u64 w_nxt(load_word(rb0 + warp + K2_WARPS, lane));
-
-	__syncthreads();					// the barrier's initialisation is visible to every waiter
-	mbar_wait(&sm.bar, 0);
-
-	uint4 v[K2_CHUNKS];
-#pragma unroll
-	for (int j = 0; j < K2_CHUNKS; ++j)
-		v[j] = *reinterpret_cast<uint4 const *>(sm.tmpl + j * 512 + lane * 16);
-
-	// What one row hands to the TMA engine: the 16-byte aligned part of [c0, c1); a ragged end goes out byte-wise.
-	u32 const off0(u32(c0 - t0));
-	u32 const n_bytes(u32(c1 - c0));
-	u32 const bulk_bytes(n_bytes & ~15u);
-	u32 const t0_32 = u32(t0), c0_32 = u32(c0), c1_32 = u32(c1);
-
-	// Edge records and labels as seen from edge 0 / label offset 0 (generic pointers into shared memory when staged).
-	edge_rec const *erecs(staged ? sm.edges - te.x : p.edges);
-	u8 const *labels(staged ? sm.labels - lab_base : p.label_chars);
-
-	u32 k(0);
+	// ---- row warps ----------------------------------------------------------------------------------------------------------
+	u32 item(warp);					// this warp's next item in the CTA's flattened (unit, row in unit) sequence
+	u32 n_issued(0);				// rows handed to the TMA engine so far: buffer n_issued & 1 is the one to fill
 #pragma unroll 1
-	for (u32 r(rb0 + warp); r < rb1; r += K2_WARPS, ++k)
+	for (u32 k(0); ; ++k)
 	{
-		u64 const w_nn(load_word(r + 2 * K2_WARPS, lane));
-		u8 *buf(sm.rows[warp][k & 1]);
-		if (k >= 2)
+		u32 const s(k % K2P_STAGES);
+		u32 const item_end((k + 1) * RC);
+		mbar_wait(&sm.full[s], (k / K2P_STAGES) & 1);
+		uint4 const hdr(sm.hdr[s]);
+		if (K2P_DONE == hdr.w) break;
+		if (item < item_end)
 		{
-			if (0 == lane) bulk_wait_read<1>();		// the copy that last read this buffer (two rows ago) is done with it
-			__syncwarp();
-		}
-#pragma unroll
-		for (int j = 0; j < K2_CHUNKS; ++j)
-			*reinterpret_cast<uint4 *>(buf + j * 512 + lane * 16) = v[j];
+			u32 const unit(hdr.w >> 2);
+			bool const words_staged(0 != (hdr.w & 2u));
+			u64 const tile(p.first_tile + unit % p.n_tiles);
+			u64 const t0(tile * K2_TCOL);
+			u64 const c0(max(t0, p.col_begin)), c1(min(t0 + K2_TCOL, p.col_end));
+			u32 const rb0(p.row_begin + (unit / p.n_tiles) * RC);
+			u32 const rb1(min(rb0 + RC, p.row_end));
+			emit_stage const &st(sm.stage[s]);
+			u32 const te_x(hdr.x), te_y(hdr.y), lab_base(hdr.z);
+			bool const staged(0 != (hdr.w & 1u)), has_edges(te_y != te_x);
+			u64 const w_lo(te_x / 64), w_hi(has_edges ? (te_y - 1) / 64 : w_lo);
+			u32 const n_words(has_edges ? u32(w_hi - w_lo + 1) : 0);
 
-		if (has_edges)
-		{
-			__syncwarp();
-#pragma unroll 1
-			for (u32 chunk(0); chunk < n_words; chunk += 32)
-			{
-				u64 const word(0 == chunk ? w_cur : load_word(r, chunk + lane));		// lane ↔ taken word chunk + lane
-				unsigned nz(__ballot_sync(0xffffffffu, 0 != word));
-#pragma unroll 1
-				while (nz)
-				{
-					// One non-empty word at a time, its 64 edges spread over the lanes: the row's patches in this word are
-					// applied side by side (taken edges of one row never overlap, so their order does not matter).
-					int const wl(__ffs(nz) - 1);
-					nz &= nz - 1;
-					u32 const bits_lo(__shfl_sync(0xffffffffu, u32(word), wl)), bits_hi(__shfl_sync(0xffffffffu, u32(word >> 32), wl));
-					u64 const e_base(64 * (w_lo + chunk + wl));
+			// The row's taken-edge words that cover the tile's edges, lane ↔ word: from the stage, or (a tile with more than
+			// 64 · K2P_WORDS edges) straight from the plan. Bits of edges outside the tile's range are masked off.
+			auto const taken_word([&](u32 const r, u32 const i) -> u64 {
+				if (i >= n_words) return 0;
+				u64 word(words_staged ? st.words[r - rb0][i % K2P_WORDS] : p.taken[u64(r) * p.We + w_lo + i]);
+				u64 const w(w_lo + i);
+				if (w == w_lo) word &= ~u64(0) << (te_x % 64);
+				if (w == w_hi && 0 != te_y % 64) word &= (u64(1) << (te_y % 64)) - 1;
+				return word;
+			});
+			u32 r(rb0 + (item - k * RC));
+
+			uint4 v[K2_CHUNKS];
 #pragma unroll
-					for (int half = 0; half < 2; ++half)
+			for (int j = 0; j < K2_CHUNKS; ++j)
+				v[j] = *reinterpret_cast<uint4 const *>(st.tmpl + j * 512 + lane * 16);
+
+			// What one row hands to the TMA engine: the 16-byte aligned part of [c0, c1); a ragged end goes out byte-wise.
+			u32 const off0(u32(c0 - t0));
+			u32 const n_bytes(u32(c1 - c0));
+			u32 const bulk_bytes(n_bytes & ~15u);
+			u32 const t0_32 = u32(t0), c0_32 = u32(c0), c1_32 = u32(c1);
+
+			// Edge records and labels as seen from edge 0 / label offset 0 (generic pointers into shared memory when staged).
+			edge_rec const *erecs(staged ? st.edges - te_x : p.edges);
+			u8 const *labels(staged ? st.labels - lab_base : p.label_chars);
+
+#pragma unroll 1
+			for (; item < item_end; item += K2P_CWARPS, r += K2P_CWARPS)
+			{
+				if (r >= rb1) continue;			// the last row chunk may be short
+				u8 *buf(sm.rows[warp][n_issued & 1]);
+				if (n_issued >= 2)
+				{
+					if (0 == lane) bulk_wait_read<1>();		// the copy that last read this buffer (two rows ago) is done with it
+					__syncwarp();
+				}
+#pragma unroll
+				for (int j = 0; j < K2_CHUNKS; ++j)
+					*reinterpret_cast<uint4 *>(buf + j * 512 + lane * 16) = v[j];
+
+				if (has_edges)
+				{
+					__syncwarp();
+#pragma unroll 1
+					for (u32 chunk(0); chunk < n_words; chunk += 32)
 					{
-						u32 const bits(half ? bits_hi : bits_lo);
-						if (0 == bits) continue;
-						bool pending(false);
-						edge_rec prec{};
-						u32 plo(0), phi(0);
-						if (bits >> lane & 1u)
+						u64 const word(taken_word(r, chunk + lane));		// lane ↔ taken word chunk + lane
+						unsigned nz(__ballot_sync(0xffffffffu, 0 != word));
+#pragma unroll 1
+						while (nz)
 						{
-							edge_rec const rec(*reinterpret_cast<edge_rec const *>(&reinterpret_cast<uint4 const *>(erecs)[e_base + 32 * half + lane]));
-							u32 const lo(max(rec.a0, c0_32)), hi(min(rec.a1, c1_32));
-							if (lo < hi)
+							// One non-empty word at a time, its 64 edges spread over the lanes: the row's patches in this word are
+							// applied side by side (taken edges of one row never overlap, so their order does not matter).
+							int const wl(__ffs(nz) - 1);
+							nz &= nz - 1;
+							u32 const bits_lo(__shfl_sync(0xffffffffu, u32(word), wl)), bits_hi(__shfl_sync(0xffffffffu, u32(word >> 32), wl));
+							u64 const e_base(64 * (w_lo + chunk + wl));
+#pragma unroll
+							for (int half = 0; half < 2; ++half)
 							{
-								if (hi - lo <= K2_SHORT_PATCH)
-									for (u32 col(lo); col < hi; ++col) buf[col - t0_32] = patch_byte(rec, labels, col);
-								else { pending = true; prec = rec; plo = lo; phi = hi; }
+								u32 const bits(half ? bits_hi : bits_lo);
+								if (0 == bits) continue;
+								bool pending(false);
+								edge_rec prec{};
+								u32 plo(0), phi(0);
+								if (bits >> lane & 1u)
+								{
+									edge_rec const rec(*reinterpret_cast<edge_rec const *>(&reinterpret_cast<uint4 const *>(erecs)[e_base + 32 * half + lane]));
+									u32 const lo(max(rec.a0, c0_32)), hi(min(rec.a1, c1_32));
+									if (lo < hi)
+									{
+										if (hi - lo <= K2_SHORT_PATCH)
+											for (u32 col(lo); col < hi; ++col) buf[col - t0_32] = patch_byte(rec, labels, col);
+										else { pending = true; prec = rec; plo = lo; phi = hi; }
+									}
+								}
+								// Long spans (large deletions / insertions) are written by the whole warp, one at a time.
+								unsigned m(__ballot_sync(0xffffffffu, pending));
+								while (m)
+								{
+									int const l(__ffs(m) - 1);
+									m &= m - 1;
+									edge_rec rec;
+									rec.a0 = __shfl_sync(0xffffffffu, prec.a0, l);
+									rec.a1 = __shfl_sync(0xffffffffu, prec.a1, l);
+									rec.label_off = __shfl_sync(0xffffffffu, prec.label_off, l);
+									rec.label_len = __shfl_sync(0xffffffffu, prec.label_len, l);
+									u32 const lo(__shfl_sync(0xffffffffu, plo, l)), hi(__shfl_sync(0xffffffffu, phi, l));
+									for (u32 col(lo + lane); col < hi; col += 32) buf[col - t0_32] = patch_byte(rec, labels, col);
+								}
 							}
-						}
-						// Long spans (large deletions / insertions) are written by the whole warp, one at a time.
-						unsigned m(__ballot_sync(0xffffffffu, pending));
-						while (m)
-						{
-							int const l(__ffs(m) - 1);
-							m &= m - 1;
-							edge_rec rec;
-							rec.a0 = __shfl_sync(0xffffffffu, prec.a0, l);
-							rec.a1 = __shfl_sync(0xffffffffu, prec.a1, l);
-							rec.label_off = __shfl_sync(0xffffffffu, prec.label_off, l);
-							rec.label_len = __shfl_sync(0xffffffffu, prec.label_len, l);
-							u32 const lo(__shfl_sync(0xffffffffu, plo, l)), hi(__shfl_sync(0xffffffffu, phi, l));
-							for (u32 col(lo + lane); col < hi; col += 32) buf[col - t0_32] = patch_byte(rec, labels, col);
 						}
 					}
 				}
+
+				fence_proxy_async_smem();
+				__syncwarp();
+				u8 *orow(p.out + u64(r - p.row_begin) * p.pitch + (c0 - p.col_begin));
+				if (0 == lane && bulk_bytes)
+				{
+					bulk_s2g(orow, buf + off0, bulk_bytes);
+					bulk_commit();
+				}
+				if (lane < n_bytes - bulk_bytes)
+					orow[bulk_bytes + lane] = buf[off0 + bulk_bytes + lane];
+				++n_issued;
 			}
 		}
-
-		fence_proxy_async_smem();
 		__syncwarp();
-		u8 *orow(p.out + u64(r - p.row_begin) * p.pitch + (c0 - p.col_begin));
-		if (0 == lane && bulk_bytes)
-		{
-			bulk_s2g(orow, buf + off0, bulk_bytes);
-			bulk_commit();
-		}
-		if (lane < n_bytes - bulk_bytes)
-			orow[bulk_bytes + lane] = buf[off0 + bulk_bytes + lane];
-		w_cur = w_nxt; w_nxt = w_nn;
+		if (0 == lane) mbar_arrive(&sm.empty[s]);		// release: this warp's reads of the stage are done
 	}
 	if (0 == lane) bulk_wait_read<0>();			// shared memory stays valid until the engine has read it
 }
@@ -430,6 +564,24 @@ int launch_resolve_rows(device_graph const &g, u64 const *d_lines, u32 const *d_
 	return 0;
 }
 
+// The unit tickets of emit_rows_kernel: one pair per (device, stream). Launches on one stream run one after the other and
+// each leaves its pair zeroed, so the pair needs no host-side reset; cudaStreamPerThread names a different stream in every
+// host thread, hence the thread id in the key.
+static int unit_tickets(int const dev, cudaStream_t const stream, u32 *&tickets)
+{
+	static std::mutex mtx;
+	static std::map<std::tuple<int, cudaStream_t, std::thread::id>, u32 *> table;
+	std::lock_guard<std::mutex> const lock(mtx);
+	u32 *&slot(table[{dev, stream, cudaStreamPerThread == stream ? std::this_thread::get_id() : std::thread::id()}]);
+	if (!slot)
+	{
+		V2M_CUDA_TRY(cudaMalloc(&slot, 2 * sizeof(u32)));
+		V2M_CUDA_TRY(cudaMemsetAsync(slot, 0, 2 * sizeof(u32), stream));
+	}
+	tickets = slot;
+	return 0;
+}
+
 int launch_emit_rows(device_graph const &g, u64 const *d_taken, u32 row_begin, u32 row_end, u64 col_begin, u64 col_end,
 	void *d_out, u64 pitch, cudaStream_t stream)
 {
@@ -442,12 +594,25 @@ int launch_emit_rows(device_graph const &g, u64 const *d_taken, u32 row_begin, u
 	p.out = static_cast<u8 *>(d_out); p.pitch = pitch;
 	u64 const last_tile((col_end - 1) / K2_TCOL);
 	u32 const n_rows(row_end - row_begin);
-	// grid.y is limited to 65535 row blocks: split if ever needed.
-	u32 const row_blocks((n_rows + K2_ROWS_PER_CTA - 1) / K2_ROWS_PER_CTA);
-	if (row_blocks > 65535) return fail(1, "too many rows in one emit_rows launch");
-	dim3 const grid(unsigned(last_tile - p.first_tile + 1), row_blocks);
+	p.n_tiles = u32(last_tile - p.first_tile + 1);
+	int dev(0), sms(0);
+	V2M_CUDA_TRY(cudaGetDevice(&dev));
+	V2M_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+	// Units: whole tiles (all rows) when there are enough of them to keep every SM equally busy; otherwise the rows are cut
+	// as well, down to one row per row warp.
+	u32 chunks((n_rows + K2P_UNIT_ROWS - 1) / K2P_UNIT_ROWS);
+	if (u64(p.n_tiles) * chunks < 4 * u64(sms))
+		chunks = std::max<u32>(chunks, std::min<u32>((n_rows + K2P_CWARPS - 1) / K2P_CWARPS, u32((4 * u64(sms) + p.n_tiles - 1) / p.n_tiles)));
+	if (char const *env = std::getenv("V2M_K2_UNIT_ROWS"))			// kernel experiments
+		if (int const v = std::atoi(env); v > 0 && v <= K2P_UNIT_ROWS) chunks = (n_rows + u32(v) - 1) / u32(v);
+	p.rows_per_unit = (n_rows + chunks - 1) / chunks;
+	p.n_row_chunks = (n_rows + p.rows_per_unit - 1) / p.rows_per_unit;
+	u64 const n_units(u64(p.n_tiles) * p.n_row_chunks);
+	if (n_units * p.rows_per_unit >= (u64(1) << 30)) return fail(1, "too many rows x tiles in one emit_rows launch");
+	if (int const st = unit_tickets(dev, stream, p.tickets)) return st;
+	unsigned const grid(unsigned(std::min<u64>(n_units, u64(sms))));
 	V2M_CUDA_TRY(cudaFuncSetAttribute(emit_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sizeof(emit_smem))));	// per device
-	emit_rows_kernel<<<grid, K2_THREADS, sizeof(emit_smem), stream>>>(p);
+	emit_rows_kernel<<<grid, K2P_THREADS, sizeof(emit_smem), stream>>>(p);
 	V2M_CHECK_LAUNCH("emit_rows_kernel");
 	return 0;
 }
