@@ -187,6 +187,34 @@ def test_rows_many_rows_blocks(v2m, tmp_path):
         assert rows[i].tobytes() == cache[h], (i, h)
 
 
+def test_rows_dense_tiles_fall_back_to_global_arrays(v2m, tmp_path):
+    """Tiles with more ALT edges, label bytes and taken-edge words than emit_rows stages in shared memory (256 edge records,
+    2 KiB of labels, 4 words per row): the row warps then read the global arrays. Many rows, so that several row chunks and
+    short last chunks occur, plus ragged column windows over the dense tiles."""
+    og = rg.random_oracle_graph(str(tmp_path), 4321, ref_len=6000, n_records=2600, n_samples=45, ploidy=2, max_indel=9, alt_freq=0.12,
+                                many_alts_prob=0.6, long_del_prob=0.01)
+    a = og.arrays()
+    A = int(a["aligned_positions"][-1])
+    E = len(a["alt_edge_targets"])
+    assert E > 3 * 256 * ((A + 4095) // 4096), (E, A)          # every tile is far over the edge cap on average
+    assert int(a["label_offsets"][-1]) > 3 * 2048 * ((A + 4095) // 4096)
+    dg, g = _device_graph(v2m, og)
+    H = a["total_copies"]
+    idx = list(range(H)) + [orc.PLOIDY_MAX]
+    plan = dg.plan_haplotypes(idx)
+    full = [og.output_sequence(h) for h in idx]
+    rows = plan.emit_rows()
+    for i in range(len(idx)):
+        assert rows[i].tobytes() == full[i], i
+    rng = np.random.default_rng(5)
+    for _ in range(8):
+        c0, c1 = sorted(int(x) for x in rng.integers(0, A + 1, 2))
+        r0, r1 = sorted(int(x) for x in rng.integers(0, len(idx) + 1, 2))
+        win = plan.emit_rows(r0, r1, c0, c1)
+        for i, r in enumerate(range(r0, r1)):
+            assert win[i].tobytes() == full[r][c0:c1], (r, c0, c1)
+
+
 def test_founder_rows_random(v2m, tmp_path):
     """Founder rows given the oracle's cut positions and matchings (K2c = compose + K2a + K2b)."""
     done = 0
