@@ -22,7 +22,12 @@
 //           was measured and dropped: half-sector stores cost read-modify-write traffic in the L2 (5.0 GB written, 4.1 ms).
 //           Also measured and dropped on c5: one persistent CTA per SM with two cp.async-filled tile buffers (2.08 ms: 16
 //           warps per SM do not cover the transpose's issue time) and 256-line tiles with 4 CTAs per SM (1.96 ms: 32-byte
-//           store runs); this kernel runs 1.61 ms there.
+//           store runs); 256 threads with two sub-tiles each, cp.async loads and 3 CTAs per SM (1.63 ms: occupancy is not
+//           the limit); this kernel runs 1.61 ms there.
+//   shapes  the destination line is C / 8 bytes long. When that is not a multiple of 32 (c5: 750,000 bytes) every other
+//           destination line starts in the middle of a sector, its 64-byte runs touch three sectors instead of two, and the
+//           kernel reaches 72 % of the copy peak; with C = 6,000,128 (or the c2 shape, or 12,000,000) it reaches 83 %
+//           (scripts/bench_transpose.py --cols …). The layout is the reference's, so the lines cannot be padded.
 //
 // Algorithmic bytes: 2 · R · C / 8 (each bit read once, written once). Roofline: HBM read + write.
 #include "common.cuh"
