@@ -99,6 +99,20 @@ __device__ __forceinline__ void bulk_s2g(void *gdst, void const *smem_src, u32 c
 		:: "l"(gdst), "r"(smem_u32(smem_src)), "r"(bytes) : "memory");
 }
 
+// The same with an L2 cache policy (createpolicy) for the written lines.
+__device__ __forceinline__ void bulk_s2g_hint(void *gdst, void const *smem_src, u32 const bytes, u64 const policy)
+{
+	asm volatile("cp.async.bulk.global.shared::cta.bulk_group.L2::cache_hint [%0], [%1], %2, %3;"
+		:: "l"(gdst), "r"(smem_u32(smem_src)), "r"(bytes), "l"(policy) : "memory");
+}
+
+__device__ __forceinline__ u64 l2_policy_evict_first()
+{
+	u64 policy;
+	asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(policy));
+	return policy;
+}
+
 __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 
 // Waits until at most t_pending of the calling thread's bulk groups have not yet finished READING their shared-memory source.

@@ -392,6 +392,7 @@ emit_rows_kernel(emit_params const p)
 	}
 
 	// ---- row warps ----------------------------------------------------------------------------------------------------------
+	u64 const store_policy(l2_policy_evict_first());		// rows are written once and never read back on the device (+1 %)
 	u32 item(warp);					// this warp's next item in the CTA's flattened (unit, row in unit) sequence
 	u32 n_issued(0);				// rows handed to the TMA engine so far: buffer n_issued & 1 is the one to fill
 #pragma unroll 1
@@ -518,7 +519,7 @@ emit_rows_kernel(emit_params const p)
 				u8 *orow(p.out + u64(r - p.row_begin) * p.pitch + (c0 - p.col_begin));
 				if (0 == lane && bulk_bytes)
 				{
-					bulk_s2g(orow, buf + off0, bulk_bytes);
+					bulk_s2g_hint(orow, buf + off0, bulk_bytes, store_policy);
 					bulk_commit();
 				}
 				if (lane < n_bytes - bulk_bytes)
