@@ -741,6 +741,7 @@ static int stream_a2m_impl(v2m_plan_t p, const char *ids, int unaligned, v2m_sin
 	std::vector<copy_piece> pieces;
 	u8 *h_buf[2] = {nullptr, nullptr};
 	u8 *d_buf[2] = {nullptr, nullptr};
+	u64 *d_row_offsets(nullptr);				// --unaligned: i · pitch for the rows of a block
 	cudaStream_t streams[2] = {nullptr, nullptr};
 	int st(V2M_OK);
 
@@ -748,11 +749,10 @@ static int stream_a2m_impl(v2m_plan_t p, const char *ids, int unaligned, v2m_sin
 		u32 const r1(std::min<u64>(n_rows, u64(r0) + block_rows));
 		if (unaligned)
 		{
-			std::vector<u64> offsets(r1 - r0);
-			for (u32 r(r0); r < r1; ++r) offsets[r - r0] = u64(r - r0) * pitch;
-			return v2m_cuda_emit_rows_unaligned(p, r0, r1, offsets.data(), h_buf[k]);	// synchronous
+			// Rows at pitch offsets like the aligned ones (the bytes between a row's end and the next pitch are not used).
+			if (int const s = launch_emit_unaligned(g, p->p.taken, p->p.prefix, r0, r1, d_row_offsets, d_buf[k], streams[k])) return s;
 		}
-		if (int const s = launch_emit_rows(g, p->p.taken, r0, r1, 0, g.A, d_buf[k], pitch, streams[k])) return s;
+		else if (int const s = launch_emit_rows(g, p->p.taken, r0, r1, 0, g.A, d_buf[k], pitch, streams[k])) return s;
 		if (cudaSuccess != cudaMemcpyAsync(h_buf[k], d_buf[k], u64(r1 - r0) * pitch, cudaMemcpyDeviceToHost, streams[k]))
 			return fail(V2M_ERR_CUDA, "write_a2m: D2H copy failed");
 		return V2M_OK;
@@ -767,6 +767,14 @@ static int stream_a2m_impl(v2m_plan_t p, const char *ids, int unaligned, v2m_sin
 			if (cudaSuccess != cudaStreamCreateWithFlags(&streams[i], cudaStreamNonBlocking)) st = fail(V2M_ERR_CUDA, "write_a2m: cudaStreamCreate failed");
 		}
 		if (st) break;
+		if (unaligned)
+		{
+			if ((st = ensure_unaligned_prefix(p))) break;
+			std::vector<u64> offsets(block_rows);
+			for (u32 i(0); i < block_rows; ++i) offsets[i] = u64(i) * pitch;
+			if ((st = dev_upload(d_row_offsets, offsets.data(), offsets.size()))) break;
+			if (cudaSuccess != cudaDeviceSynchronize()) { st = fail(V2M_ERR_CUDA, "write_a2m: upload of the row offsets failed"); break; }	// the streams below do not wait for the default stream
+		}
 
 		char const *id(ids);
 		if ((st = produce(0, 0))) break;
@@ -824,6 +832,7 @@ static int stream_a2m_impl(v2m_plan_t p, const char *ids, int unaligned, v2m_sin
 		cudaFree(d_buf[i]);
 		if (h_buf[i]) cudaFreeHost(h_buf[i]);
 	}
+	cudaFree(d_row_offsets);
 	// Leave the descriptor where sequential writes would have left it.
 	if (positional) { int const cst(mapping.close(V2M_OK == st)); if (!st) st = cst; }
 	return st;
