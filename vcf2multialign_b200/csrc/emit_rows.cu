@@ -25,6 +25,7 @@
 #include <mutex>
 #include <thread>
 #include <tuple>
+#include <type_traits>
 
 #include "common.cuh"
 #include "device_graph.hh"
@@ -283,13 +284,6 @@ struct emit_params
 	u64				pitch;
 };
 
-// `labels` is the label store seen from label offset 0: the global array, or the tile's staged window shifted back.
-__device__ __forceinline__ u8 patch_byte(edge_rec const &rec, u8 const *labels, u32 const col)
-{
-	u32 const k(col - rec.a0);
-	return k < rec.label_len ? labels[rec.label_off + k] : u8('-');
-}
-
 __global__ void __launch_bounds__(K2P_THREADS, 1)
 emit_rows_kernel(emit_params const p)
 {
@@ -313,7 +307,7 @@ emit_rows_kernel(emit_params const p)
 		// One unit ahead of itself: the ticket and the tile's edge range of unit k + 1 are asked for while the words of unit k
 		// are on their way, so that the warp spends one memory latency per unit, not three.
 		auto const next_ticket([&]() -> u32 { return __shfl_sync(0xffffffffu, 0 == lane ? atomicAdd(p.tickets, 1u) : 0u, 0); });
-		auto const edges_of([&](u32 const u) -> uint2 { return u < n_units ? p.tile_edges[p.first_tile + u % p.n_tiles] : make_uint2(0, 0); });
+		auto const edges_of([&](u32 const u) -> uint2 { return u < n_units ? p.tile_edges[p.first_tile + u / p.n_row_chunks] : make_uint2(0, 0); });
 		u32 unit(next_ticket());
 		uint2 te(edges_of(unit));
 #pragma unroll 1
@@ -332,7 +326,7 @@ emit_rows_kernel(emit_params const p)
 				break;
 			}
 			u32 const unit_after(next_ticket());
-			u64 const tile(p.first_tile + unit % p.n_tiles);
+			u64 const tile(p.first_tile + unit / p.n_row_chunks);
 			u64 const w_lo(te.x / 64);
 			u32 const n_words(te.y != te.x ? u32((te.y - 1) / 64 - w_lo + 1) : 0);
 			bool const words_staged(n_words <= K2P_WORDS);
@@ -357,7 +351,7 @@ emit_rows_kernel(emit_params const p)
 			bool const gather(words_staged && 0 != n_words);
 			if (gather)
 			{
-				u32 const rb0(p.row_begin + (unit / p.n_tiles) * RC);
+				u32 const rb0(p.row_begin + (unit % p.n_row_chunks) * RC);
 				u32 const rb1(min(rb0 + RC, p.row_end));
 #pragma unroll
 				for (int j = 0; j < PER_LANE; ++j)
@@ -407,10 +401,10 @@ emit_rows_kernel(emit_params const p)
 		{
 			u32 const unit(hdr.w >> 2);
 			bool const words_staged(0 != (hdr.w & 2u));
-			u64 const tile(p.first_tile + unit % p.n_tiles);
+			u64 const tile(p.first_tile + unit / p.n_row_chunks);
 			u64 const t0(tile * K2_TCOL);
 			u64 const c0(max(t0, p.col_begin)), c1(min(t0 + K2_TCOL, p.col_end));
-			u32 const rb0(p.row_begin + (unit / p.n_tiles) * RC);
+			u32 const rb0(p.row_begin + (unit % p.n_row_chunks) * RC);
 			u32 const rb1(min(rb0 + RC, p.row_end));
 			emit_stage const &st(sm.stage[s]);
 			u32 const te_x(hdr.x), te_y(hdr.y), lab_base(hdr.z);
@@ -418,16 +412,6 @@ emit_rows_kernel(emit_params const p)
 			u64 const w_lo(te_x / 64), w_hi(has_edges ? (te_y - 1) / 64 : w_lo);
 			u32 const n_words(has_edges ? u32(w_hi - w_lo + 1) : 0);
 
-			// The row's taken-edge words that cover the tile's edges, lane ↔ word: from the stage, or (a tile with more than
-			// 64 · K2P_WORDS edges) straight from the plan. Bits of edges outside the tile's range are masked off.
-			auto const taken_word([&](u32 const r, u32 const i) -> u64 {
-				if (i >= n_words) return 0;
-				u64 word(words_staged ? st.words[r - rb0][i % K2P_WORDS] : p.taken[u64(r) * p.We + w_lo + i]);
-				u64 const w(w_lo + i);
-				if (w == w_lo) word &= ~u64(0) << (te_x % 64);
-				if (w == w_hi && 0 != te_y % 64) word &= (u64(1) << (te_y % 64)) - 1;
-				return word;
-			});
 			u32 r(rb0 + (item - k * RC));
 
 			uint4 v[K2_CHUNKS];
@@ -441,91 +425,124 @@ emit_rows_kernel(emit_params const p)
 			u32 const bulk_bytes(n_bytes & ~15u);
 			u32 const t0_32 = u32(t0), c0_32 = u32(c0), c1_32 = u32(c1);
 
-			// Edge records and labels as seen from edge 0 / label offset 0 (generic pointers into shared memory when staged).
-			edge_rec const *erecs(staged ? st.edges - te_x : p.edges);
-			u8 const *labels(staged ? st.labels - lab_base : p.label_chars);
+			// Which bits of taken word i (lane ↔ word) belong to edges of this tile.
+			auto const tile_bits([&](u32 const i) -> u64 {
+				if (i >= n_words) return 0;
+				u64 keep(~u64(0));
+				u64 const w(w_lo + i);
+				if (w == w_lo) keep &= ~u64(0) << (te_x % 64);
+				if (w == w_hi && 0 != te_y % 64) keep &= (u64(1) << (te_y % 64)) - 1;
+				return keep;
+			});
+			u64 const keep0(tile_bits(lane));
+
+			// The rows of this warp in this unit. FAST: everything the patches read was staged (the common case), so it is
+			// addressed as shared memory; otherwise edge records, labels and / or taken words come from the global arrays.
+			auto const write_rows([&](auto const fast_tag) {
+				constexpr bool FAST = decltype(fast_tag)::value;
+				auto const edge_record([&](u32 const e) -> edge_rec {
+					uint4 const q(FAST ? reinterpret_cast<uint4 const *>(st.edges)[e - te_x]
+						: (staged ? reinterpret_cast<uint4 const *>(st.edges)[e - te_x] : reinterpret_cast<uint4 const *>(p.edges)[e]));
+					return edge_rec{q.x, q.y, q.z, q.w};
+				});
+				auto const patch([&](edge_rec const &rec, u32 const col) -> u8 {
+					u32 const k(col - rec.a0);
+					if (k >= rec.label_len) return u8('-');
+					if (FAST || staged) return st.labels[rec.label_off - lab_base + k];
+					return p.label_chars[rec.label_off + k];
+				});
 
 #pragma unroll 1
-			for (; item < item_end; item += K2P_CWARPS, r += K2P_CWARPS)
-			{
-				if (r >= rb1) continue;			// the last row chunk may be short
-				u8 *buf(sm.rows[warp][n_issued & 1]);
-				if (n_issued >= 2)
+				for (; item < item_end; item += K2P_CWARPS, r += K2P_CWARPS)
 				{
-					if (0 == lane) bulk_wait_read<1>();		// the copy that last read this buffer (two rows ago) is done with it
-					__syncwarp();
-				}
-#pragma unroll
-				for (int j = 0; j < K2_CHUNKS; ++j)
-					*reinterpret_cast<uint4 *>(buf + j * 512 + lane * 16) = v[j];
-
-				if (has_edges)
-				{
-					__syncwarp();
-#pragma unroll 1
-					for (u32 chunk(0); chunk < n_words; chunk += 32)
+					if (r >= rb1) continue;			// the last row chunk may be short
+					u8 *buf(sm.rows[warp][n_issued & 1]);
+					if (n_issued >= 2)
 					{
-						u64 const word(taken_word(r, chunk + lane));		// lane ↔ taken word chunk + lane
-						unsigned nz(__ballot_sync(0xffffffffu, 0 != word));
-#pragma unroll 1
-						while (nz)
-						{
-							// One non-empty word at a time, its 64 edges spread over the lanes: the row's patches in this word are
-							// applied side by side (taken edges of one row never overlap, so their order does not matter).
-							int const wl(__ffs(nz) - 1);
-							nz &= nz - 1;
-							u32 const bits_lo(__shfl_sync(0xffffffffu, u32(word), wl)), bits_hi(__shfl_sync(0xffffffffu, u32(word >> 32), wl));
-							u64 const e_base(64 * (w_lo + chunk + wl));
+						if (0 == lane) bulk_wait_read<1>();		// the copy that last read this buffer (two rows ago) is done with it
+						__syncwarp();
+					}
 #pragma unroll
-							for (int half = 0; half < 2; ++half)
+					for (int j = 0; j < K2_CHUNKS; ++j)
+						*reinterpret_cast<uint4 *>(buf + j * 512 + lane * 16) = v[j];
+
+					if (has_edges)
+					{
+						__syncwarp();
+#pragma unroll 1
+						for (u32 chunk(0); chunk < n_words; chunk += 32)
+						{
+							// lane ↔ taken word chunk + lane
+							u64 word;
+							if (FAST) word = st.words[r - rb0][lane % K2P_WORDS] & keep0;
+							else
 							{
-								u32 const bits(half ? bits_hi : bits_lo);
-								if (0 == bits) continue;
-								bool pending(false);
-								edge_rec prec{};
-								u32 plo(0), phi(0);
-								if (bits >> lane & 1u)
+								u32 const i(chunk + lane);
+								word = i < n_words ? (words_staged ? st.words[r - rb0][i % K2P_WORDS] : p.taken[u64(r) * p.We + w_lo + i]) & tile_bits(i) : 0;
+							}
+							unsigned nz(__ballot_sync(0xffffffffu, 0 != word));
+#pragma unroll 1
+							while (nz)
+							{
+								// One non-empty word at a time, its 64 edges spread over the lanes: the row's patches in this word are
+								// applied side by side (taken edges of one row never overlap, so their order does not matter).
+								int const wl(__ffs(nz) - 1);
+								nz &= nz - 1;
+								u32 const bits_lo(__shfl_sync(0xffffffffu, u32(word), wl)), bits_hi(__shfl_sync(0xffffffffu, u32(word >> 32), wl));
+								u32 const e_base(64 * (u32(w_lo) + chunk + u32(wl)));			// edge indices fit 32 bits (tile_edges)
+#pragma unroll
+								for (int half = 0; half < 2; ++half)
 								{
-									edge_rec const rec(*reinterpret_cast<edge_rec const *>(&reinterpret_cast<uint4 const *>(erecs)[e_base + 32 * half + lane]));
-									u32 const lo(max(rec.a0, c0_32)), hi(min(rec.a1, c1_32));
-									if (lo < hi)
+									u32 const bits(half ? bits_hi : bits_lo);
+									if (0 == bits) continue;
+									bool pending(false);
+									edge_rec prec{};
+									u32 plo(0), phi(0);
+									if (bits >> lane & 1u)
 									{
-										if (hi - lo <= K2_SHORT_PATCH)
-											for (u32 col(lo); col < hi; ++col) buf[col - t0_32] = patch_byte(rec, labels, col);
-										else { pending = true; prec = rec; plo = lo; phi = hi; }
+										edge_rec const rec(edge_record(e_base + 32 * half + lane));
+										u32 const lo(max(rec.a0, c0_32)), hi(min(rec.a1, c1_32));
+										if (lo < hi)
+										{
+											if (hi - lo <= K2_SHORT_PATCH)
+												for (u32 col(lo); col < hi; ++col) buf[col - t0_32] = patch(rec, col);
+											else { pending = true; prec = rec; plo = lo; phi = hi; }
+										}
 									}
-								}
-								// Long spans (large deletions / insertions) are written by the whole warp, one at a time.
-								unsigned m(__ballot_sync(0xffffffffu, pending));
-								while (m)
-								{
-									int const l(__ffs(m) - 1);
-									m &= m - 1;
-									edge_rec rec;
-									rec.a0 = __shfl_sync(0xffffffffu, prec.a0, l);
-									rec.a1 = __shfl_sync(0xffffffffu, prec.a1, l);
-									rec.label_off = __shfl_sync(0xffffffffu, prec.label_off, l);
-									rec.label_len = __shfl_sync(0xffffffffu, prec.label_len, l);
-									u32 const lo(__shfl_sync(0xffffffffu, plo, l)), hi(__shfl_sync(0xffffffffu, phi, l));
-									for (u32 col(lo + lane); col < hi; col += 32) buf[col - t0_32] = patch_byte(rec, labels, col);
+									// Long spans (large deletions / insertions) are written by the whole warp, one at a time.
+									unsigned m(__ballot_sync(0xffffffffu, pending));
+									while (m)
+									{
+										int const l(__ffs(m) - 1);
+										m &= m - 1;
+										edge_rec rec;
+										rec.a0 = __shfl_sync(0xffffffffu, prec.a0, l);
+										rec.a1 = __shfl_sync(0xffffffffu, prec.a1, l);
+										rec.label_off = __shfl_sync(0xffffffffu, prec.label_off, l);
+										rec.label_len = __shfl_sync(0xffffffffu, prec.label_len, l);
+										u32 const lo(__shfl_sync(0xffffffffu, plo, l)), hi(__shfl_sync(0xffffffffu, phi, l));
+										for (u32 col(lo + lane); col < hi; col += 32) buf[col - t0_32] = patch(rec, col);
+									}
 								}
 							}
 						}
 					}
-				}
 
-				fence_proxy_async_smem();
-				__syncwarp();
-				u8 *orow(p.out + u64(r - p.row_begin) * p.pitch + (c0 - p.col_begin));
-				if (0 == lane && bulk_bytes)
-				{
-					bulk_s2g_hint(orow, buf + off0, bulk_bytes, store_policy);
-					bulk_commit();
+					fence_proxy_async_smem();
+					__syncwarp();
+					u8 *orow(p.out + u64(r - p.row_begin) * p.pitch + (c0 - p.col_begin));
+					if (0 == lane && bulk_bytes)
+					{
+						bulk_s2g_hint(orow, buf + off0, bulk_bytes, store_policy);
+						bulk_commit();
+					}
+					if (lane < n_bytes - bulk_bytes)
+						orow[bulk_bytes + lane] = buf[off0 + bulk_bytes + lane];
+					++n_issued;
 				}
-				if (lane < n_bytes - bulk_bytes)
-					orow[bulk_bytes + lane] = buf[off0 + bulk_bytes + lane];
-				++n_issued;
-			}
+			});
+			if (staged && words_staged) write_rows(std::true_type{});
+			else write_rows(std::false_type{});
 		}
 		__syncwarp();
 		if (0 == lane) mbar_arrive(&sm.empty[s]);		// release: this warp's reads of the stage are done
