@@ -483,8 +483,9 @@ namespace {
 // 16-byte pitch), but not at a multiple of 4 KiB, which puts the same columns of all rows on the same DRAM channels (−13 %).
 static u64 device_row_pitch(u64 const row_bytes)
 {
-	u64 pitch((std::max<u64>(row_bytes, 1) + 127) & ~u64(127));
-	if (0 == pitch % 4096) pitch += 128;
+	static u64 const align([] { char const *env(std::getenv("V2M_ROW_PITCH_ALIGN")); u64 const v(env ? std::strtoull(env, nullptr, 10) : 0); return (v >= 16 && 0 == (v & (v - 1))) ? v : u64(128); }());	// experiments
+	u64 pitch((std::max<u64>(row_bytes, 1) + align - 1) & ~(align - 1));
+	if (0 == pitch % 4096) pitch += align;
 	return pitch;
 }
 
