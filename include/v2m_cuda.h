@@ -125,7 +125,7 @@ int v2m_cuda_plan_row_lengths(v2m_plan_t p, int unaligned, uint64_t *out /* [n_r
  * header, no newline): out[(r - row_begin) * pitch + (c - col_begin)].
  * Device variant: d_out must be 16-byte aligned, pitch % 16 == 0, col_begin % 16 == 0; asynchronous on `stream`.
  * Fastest with rows starting on 128-byte lines (pitch % 128 == 0, but not a multiple of 4096) and 64 or more rows per
- * call; launches on one stream must not be issued from several host threads at once. */
+ * call. */
 int v2m_cuda_emit_rows_device(v2m_plan_t p, uint32_t row_begin, uint32_t row_end, uint64_t col_begin, uint64_t col_end,
                               void *d_out, uint64_t pitch, void *stream);
 /* Host variant: kernels fill device tiles that are copied into `out` (any host memory; pinned is faster). */
