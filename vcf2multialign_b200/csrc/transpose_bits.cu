@@ -23,13 +23,17 @@
 //           Also measured and dropped on c5: one persistent CTA per SM with two cp.async-filled tile buffers (2.08 ms: 16
 //           warps per SM do not cover the transpose's issue time) and 256-line tiles with 4 CTAs per SM (1.96 ms: 32-byte
 //           store runs); 256 threads with two sub-tiles each, cp.async loads and 3 CTAs per SM (1.63 ms: occupancy is not
-//           the limit); this kernel runs 1.61 ms there.
+//           the limit); 1024-line × 512-bit tiles whose stores are single 128-byte runs (transpose_bits_tall_kernel below:
+//           1.62 ms — what the longer runs save on the misaligned destination lines, the 64-byte source pieces lose);
+//           this kernel runs 1.61 ms there.
 //   shapes  the destination line is C / 8 bytes long. When that is not a multiple of 32 (c5: 750,000 bytes) every other
 //           destination line starts in the middle of a sector, its 64-byte runs touch three sectors instead of two, and the
 //           kernel reaches 72 % of the copy peak; with C = 6,000,128 (or the c2 shape, or 12,000,000) it reaches 83 %
 //           (scripts/bench_transpose.py --cols …). The layout is the reference's, so the lines cannot be padded.
 //
 // Algorithmic bytes: 2 · R · C / 8 (each bit read once, written once). Roofline: HBM read + write.
+#include <cstdlib>
+
 #include "common.cuh"
 
 namespace v2m {
@@ -101,10 +105,88 @@ transpose_bits_kernel(u64 const * __restrict__ src, u32 * __restrict__ dst, u64 
 
 
 
+// The same transpose on tiles of 1024 source lines × 512 bits (16 words): a warp's store is one 128-byte run of one
+// destination line instead of two 64-byte runs, which halves the partial-sector stores when destination lines are not
+// a multiple of 32 bytes long. Lane ↔ line group (32 of them), warp ↔ word column (16). Shared layout, in 32-bit words:
+// line l at l · 16 + 16 · (l >> 9), its word c at position c ^ ((l >> 5) & 15): the 32 lanes of a transposing read (lines
+// 32 · lane + i, one column) hit 32 distinct banks, and the loading warps' 8-byte stores stay conflict-free.
+constexpr int K1T_TC = 1024;
+constexpr int K1T_TW = 16;
+
+__global__ void __launch_bounds__(K1_THREADS, 2)
+transpose_bits_tall_kernel(u64 const * __restrict__ src, u32 * __restrict__ dst, u64 const R64, u64 const C)
+{
+	extern __shared__ __align__(16) u64 tile[];					// K1T_TC · K1T_TW words + 16 words of padding
+	u64 const c0(u64(blockIdx.y) * K1T_TC);
+	u64 const p0(u64(blockIdx.x) * (K1T_TW / 2));				// first 64-bit word (pair) of the row band
+	unsigned const tid(threadIdx.x);
+
+	{
+		unsigned const q(tid & 7);								// pair within the 64-byte piece of a line
+		unsigned const l_in_pass(tid >> 3);						// 64 lines per pass
+		bool const pair_ok(p0 + q < R64);
+		u64 vals[K1T_TC / 64];
+#pragma unroll
+		for (int p = 0; p < K1T_TC / 64; ++p)
+		{
+			u64 const line(c0 + 64 * p + l_in_pass);
+			vals[p] = (pair_ok && line < C) ? __ldg(src + line * R64 + p0 + q) : 0;
+		}
+#pragma unroll
+		for (int p = 0; p < K1T_TC / 64; ++p)
+		{
+			unsigned const l(64 * p + l_in_pass);
+			unsigned const sw((l >> 5) & 15);
+			u64 const v(vals[p]);
+			tile[l * 8 + 8 * (l >> 9) + (q ^ (sw >> 1))] = (sw & 1) ? (v >> 32 | v << 32) : v;
+		}
+	}
+	__syncthreads();
+
+	unsigned const lane(tid & 31), yw(tid >> 5);				// lane = line group, yw = word column
+	u32 const *tile32(reinterpret_cast<u32 const *>(tile));
+	u32 a[32];
+	{
+		unsigned const base(32 * lane * 16 + 16 * (lane >> 4) + (yw ^ (lane & 15)));
+#pragma unroll
+		for (int i = 0; i < 32; ++i)
+			a[i] = tile32[base + i * 16];
+	}
+	transpose32(a);
+
+	u64 const C32(C / 32);
+	u64 const xw(c0 / 32 + lane);
+	u64 const r0(64 * p0 + 32 * yw);
+	if (xw < C32 && r0 < 64 * R64)
+	{
+		u32 *out(dst + r0 * C32 + xw);
+#pragma unroll
+		for (int j = 0; j < 32; ++j)
+			out[u64(j) * C32] = a[j];
+	}
+}
+
+
 int launch_transpose_bits(void const *d_src, u64 rows, u64 cols, void *d_dst, cudaStream_t stream)
 {
 	if (0 == cols || 0 == rows) return 0;
 	u64 const R64(rows / 64);
+	static int const force([] { char const *env(std::getenv("V2M_K1_TALL")); return env ? std::atoi(env) : -1; }());	// experiments: 0 / 1
+	// Measured (scripts/bench_transpose.py, V2M_K1_TALL=0/1): the tall tiles win when the matrix has at most 512 rows (their
+	// 512-bit band wastes less of a short line: 64 × 4,096,000 runs 2.6 × faster) and when destination lines are an odd
+	// multiple of 8 bytes long (5056 × 3,000,000: 68 % against 61 % of the copy peak); they lose 6 points on sector-aligned
+	// destination lines (their 64-byte source pieces straddle more sectors) and tie on c5.
+	bool const tall(force >= 0 ? 1 == force : (rows <= 512 || 0 != (cols / 8) % 16));
+	if (tall)
+	{
+		dim3 const grid(unsigned((R64 + K1T_TW / 2 - 1) / (K1T_TW / 2)), unsigned((cols + K1T_TC - 1) / K1T_TC));
+		if (grid.y > 65535u) return fail(1, "transpose_bits: too many source lines in one launch");
+		constexpr int smem_bytes((K1T_TC * K1T_TW + 16) * sizeof(u32));
+		V2M_CUDA_TRY(cudaFuncSetAttribute(transpose_bits_tall_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
+		transpose_bits_tall_kernel<<<grid, K1_THREADS, smem_bytes, stream>>>(static_cast<u64 const *>(d_src), static_cast<u32 *>(d_dst), R64, cols);
+		V2M_CHECK_LAUNCH("transpose_bits_tall_kernel");
+		return 0;
+	}
 	dim3 const grid(unsigned((R64 + K1_TW / 2 - 1) / (K1_TW / 2)), unsigned((cols + K1_TC - 1) / K1_TC));
 	if (grid.y > 65535u) return fail(1, "transpose_bits: more than 33,553,920 source lines in one launch");
 	constexpr int smem_bytes(K1_TC * (K1_TW / 2) * sizeof(u64));
