@@ -114,9 +114,15 @@ def main():
 
     # founder rows (K2c + K2a + K2b), device resident
     assigned = m
-    t0 = time.perf_counter()
-    plan = dg.plan_founders(cuts, np.concatenate([np.full((n_seg, 1), v2m.PLOIDY_MAX, np.uint32), assigned], axis=1))
-    out["plan_founders_s"] = time.perf_counter() - t0
+    rows_assigned = np.concatenate([np.full((n_seg, 1), v2m.PLOIDY_MAX, np.uint32), assigned], axis=1)
+    plan = None
+    for _ in range(args.iters):                # best of iters, like the two calls above (the host side of this box is noisy)
+        if plan is not None:
+            plan.close()
+        t0 = time.perf_counter()
+        plan = dg.plan_founders(cuts, rows_assigned)
+        dt = time.perf_counter() - t0
+        out["plan_founders_s"] = min(out.get("plan_founders_s", dt), dt)
     n_rows = plan.row_count()
     pitch = (A + 15) // 16 * 16
     d_out = L.v2m_cuda_device_alloc(n_rows * pitch)

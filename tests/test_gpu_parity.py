@@ -54,7 +54,9 @@ def test_transpose_property_vs_oracle(v2m, seed):
     assert np.array_equal(v2m.transpose_matrix(got, cols, rows), src)
 
 
-@pytest.mark.parametrize("rows,cols", [(64, 64), (64, 4096), (4096, 64), (5056, 2112), (1088, 1600), (960, 576), (2112, 5056)])
+# Both kernels: tall tiles are chosen for rows <= 512 or (cols / 8) % 16 != 0, the 512-line tiles otherwise.
+@pytest.mark.parametrize("rows,cols", [(64, 64), (64, 4096), (4096, 64), (5056, 2112), (1088, 1600), (960, 576), (2112, 5056),
+                                       (1024, 256), (5056, 2176), (576, 1152), (4096, 128), (640, 3200), (512, 2048), (448, 1280)])
 def test_transpose_tile_edges(v2m, rows, cols):
     """Shapes around the 512-line × 1024-row tile borders, incl. the c2/c4 row count (5056 = 4·1024 + 960)."""
     rng = np.random.default_rng(rows * 7 + cols)
