@@ -646,6 +646,48 @@ def test_ingest_genotypes_rejects_bad_allele(v2m):
     assert not words.any()                               # the only ALT has no edge
 
 
+def test_ingest_genotypes_vector_kernel_allele_check(v2m):
+    """H % 8 == 0 takes the 128-bit-load kernel, whose range check is a packed maximum of value + 1 (mod 2^16): every bad value
+    at every position of a lane's 8 values and in every load of a warp is caught, and 0, NULL and the last ALT pass."""
+    H, n_alts = 2056, 3                                  # three warps per record, the last one partial
+    ok = np.zeros((2, H), np.uint16)
+    ok[0, ::3] = v2m.GT_NULL
+    ok[0, 1::3] = n_alts
+    ok[1, :] = v2m.GT_NULL
+    ok[1, 5::7] = 1
+    words, _ = v2m.paths_from_genotypes(ok, [0, n_alts, 2 * n_alts], list(range(2 * n_alts)), 2112, 64)
+    w = np.asarray(words).reshape(-1)                    # edge-major lines of 2112 / 64 words
+    bits = np.unpackbits(w.view(np.uint8), bitorder="little").reshape(64, 2112)
+    assert (bits[n_alts - 1, :H] == (ok[0] == n_alts)).all() and (bits[n_alts, :H] == (ok[1] == 1)).all()
+    assert bits.sum() == (ok[0] == n_alts).sum() + (ok[1] == 1).sum()
+    for pos in (0, 1, 6, 7, 255, 256, 1023, 1024, 1531, 2048, 2055):
+        for bad in (n_alts + 1, 0x7fff, 0x8000, 0xfffe):
+            gt = ok.copy()
+            gt[1, pos] = bad
+            with pytest.raises(v2m.V2MError):
+                v2m.paths_from_genotypes(gt, [0, n_alts, 2 * n_alts], list(range(2 * n_alts)), 2112, 64)
+
+
+def test_ingest_genotypes_alt_numbers_beyond_half_precision(v2m):
+    """ALT numbers up to 0x7bff are matched with half-precision compares (exact for positive finite patterns, subnormals
+    included), larger ones — infinities and NaNs as binary16 — with integer compares: both sides of the switch, and the
+    values that only differ from them in the sign bit or the low bit, land in the right edge columns."""
+    alts = [1, 2, 0x03ff, 0x0400, 0x3c00, 0x7bfe, 0x7bff, 0x7c00, 0x7c01, 0x8000, 0x8001, 0xbc00, 0xfc00, 0xfffe]
+    n_alts = 0xfffe
+    gt = np.zeros((1, 64), np.uint16)
+    gt[0, : 3 * len(alts)] = np.repeat(np.array(alts, np.uint16), 3)
+    gt[0, 60:] = v2m.GT_NULL
+    eba = np.full(n_alts, v2m.EDGE_MAX, np.uint64)
+    for k, a in enumerate(alts):
+        eba[a - 1] = k
+    words, _ = v2m.paths_from_genotypes(gt, [0, n_alts], eba, 64, 64)
+    bits = np.unpackbits(np.asarray(words).view(np.uint8), bitorder="little").reshape(64, 64)
+    want = np.zeros((64, 64), np.uint8)
+    for k, a in enumerate(alts):
+        want[k, 3 * k: 3 * k + 3] = 1
+    assert (bits == want).all()
+
+
 # ---- reference-format graph files → device rows (SURVEY §8 f3) --------------------------------------------------------------
 def test_rows_from_reference_format_graph_files(v2m, expected, golden_dir):
     """A graph archive as a stock vcf2multialign writes it (--output-graph; here written by the real cereal headers) is loaded,

@@ -21,6 +21,8 @@
 #include <thread>
 #include <vector>
 
+#include <cuda_fp16.h>
+
 #include "../../include/v2m_cuda.h"
 #include "common.cuh"
 
@@ -88,6 +90,12 @@ __device__ __forceinline__ u32 eq_halves(u32 const x, u32 const pattern)
 	return ~(((t & 0x7fff7fffu) + 0x7fff7fffu) | t) & 0x80008000u;
 }
 
+// Both 16-bit halves of x incremented modulo 2^16 (no carry between the halves).
+__device__ __forceinline__ u32 inc_halves(u32 const x)
+{
+	return ((x & 0x7fff7fffu) + 0x00010001u) ^ (x & 0x80008000u);
+}
+
 struct eq4 { u32 x, y, z, w; };
 __device__ __forceinline__ eq4 eq_halves4(uint4 const &v, u32 const pattern)
 {
@@ -99,6 +107,48 @@ __device__ __forceinline__ u32 gather8(eq4 const &m)
 {
 	u32 const r((m.x >> 15) | (m.y >> 13) | (m.z >> 11) | (m.w >> 9));		// low halves → bits 0, 2, 4, 6; high halves → 16, 18, 20, 22
 	return (r & 0x55u) | ((r >> 15) & 0xaau);
+}
+
+// The same 8 bits through the half-precision compare unit: HSET2.BM gives 0xffff per equal half in one instruction instead
+// of four. As binary16 numbers two halves compare equal exactly when their bits are equal as long as the pattern is a
+// positive finite number, i.e. 1 … 0x7bff (subnormals are not flushed; NaN patterns never match, -0 only matches 0):
+// ALT numbers from 0x7c00 on take the integer compares above.
+__device__ __forceinline__ u32 heq_mask(u32 const x, u32 const pattern)
+{
+	__half2 a, b;
+	memcpy(&a, &x, 4);
+	memcpy(&b, &pattern, 4);
+	return __heq2_mask(a, b);
+}
+
+template <bool t_half>
+__device__ __forceinline__ u32 match8(uint4 const &v, u32 const pattern)
+{
+	if constexpr (t_half)
+	{
+		u32 const r((heq_mask(v.x, pattern) & 0x00020001u) | (heq_mask(v.y, pattern) & 0x00080004u)
+			| (heq_mask(v.z, pattern) & 0x00200010u) | (heq_mask(v.w, pattern) & 0x00800040u));
+		return (r | (r >> 16)) & 0xffu;						// low halves → bits 0, 2, 4, 6; high halves (bits 17 … 23) → 1, 3, 5, 7
+	}
+	else
+		return gather8(eq_halves4(v, pattern));
+}
+
+// Word `lane` of the 1,024-copy piece of one ALT's edge column.
+template <bool t_half>
+__device__ __forceinline__ u32 column_word(uint4 const (&v)[4], u32 const pattern, unsigned const lane)
+{
+	u32 mine(0);
+#pragma unroll
+	for (int i = 0; i < 4; ++i)
+	{
+		u32 w(match8 <t_half>(v[i], pattern) << (8 * (lane & 3)));
+		w |= __shfl_xor_sync(0xffffffffu, w, 1);
+		w |= __shfl_xor_sync(0xffffffffu, w, 2);						// lanes 4g … 4g+3 hold word 8i + g of the block
+		u32 const t(__shfl_sync(0xffffffffu, w, 4 * (lane & 7)));		// lane L reads word 8i + L % 8
+		if (int(lane >> 3) == i) mine = t;
+	}
+	return mine;
 }
 
 __global__ void __launch_bounds__(256)
@@ -122,38 +172,28 @@ ingest_genotypes_kernel(unsigned short const * __restrict__ gt, u64 const n_reco
 		u32 const h0(wb * 1024 + i * 256 + lane * 8);
 		v[i] = (h0 < H) ? ld_nc_v4(row + h0) : make_uint4(0, 0, 0, 0);
 	}
-	// :399 — every value must be 0, NULL or one of the record's ALTs: `known` collects the halves accounted for.
-	u32 known[4];
+	// :399 — every value must be 0, NULL or one of the record's ALTs, i.e. value + 1 (mod 2^16: NULL becomes 0) must not
+	// exceed n_alts + 1. One packed increment per word and a running packed maximum (VIMNMX3.U16x2) cost ~60 instructions
+	// per warp; collecting the matched halves per ALT next to tests against 0 and NULL cost ~200 of the kernel's 397.
+	u32 vmax(0);
 #pragma unroll
 	for (int i = 0; i < 4; ++i)
 	{
-		eq4 const z(eq_halves4(v[i], 0u)), n(eq_halves4(v[i], 0xffffffffu));
-		// the four words' bits 15 / 31 packed into bits 0–3 / 16–19 of one register
-		known[i] = ((z.x | n.x) >> 15) | ((z.y | n.y) >> 14) | ((z.z | n.z) >> 13) | ((z.w | n.w) >> 12);
+		vmax = __vimax3_u16x2(vmax, inc_halves(v[i].x), inc_halves(v[i].y));
+		vmax = __vimax3_u16x2(vmax, inc_halves(v[i].z), inc_halves(v[i].w));
 	}
 	u32 const word_mine(wb * 32 + lane);
 	for (u32 a(0); a < n_alts; ++a)
 	{
 		u64 const edge(edges_by_alt[a0 + a]);
 		u32 const pattern((a + 1) | ((a + 1) << 16));
-		u32 mine(0);
-#pragma unroll
-		for (int i = 0; i < 4; ++i)
-		{
-			eq4 const m(eq_halves4(v[i], pattern));
-			known[i] |= (m.x >> 15) | (m.y >> 14) | (m.z >> 13) | (m.w >> 12);
-			u32 w(gather8(m) << (8 * (lane & 3)));
-			w |= __shfl_xor_sync(0xffffffffu, w, 1);
-			w |= __shfl_xor_sync(0xffffffffu, w, 2);						// lanes 4g … 4g+3 hold word 8i + g of the block
-			u32 const t(__shfl_sync(0xffffffffu, w, 4 * (lane & 7)));		// lane L reads word 8i + L % 8
-			if (int(lane >> 3) == i) mine = t;
-		}
+		u32 const mine(a + 1 < 0x7c00u ? column_word <true>(v, pattern, lane) : column_word <false>(v, pattern, lane));		// warp-uniform
 		if (EDGE_NONE == edge) continue;
 		if (edge >= e_pad) { atomicOr(bad, 2u); continue; }
 		if (word_mine < Wh32) paths32[edge * Wh32 + word_mine] = mine;
 	}
-	// bits 0–3 (low halves) and 16–19 (high halves) of known[i] must all be set
-	if (0x000f000fu != (known[0] & known[1] & known[2] & known[3] & 0x000f000fu)) atomicOr(bad, 1u);
+	u32 const limit(min(n_alts, 0xfffeu) + 1);
+	if ((vmax & 0xffffu) > limit || (vmax >> 16) > limit) atomicOr(bad, 1u);
 }
 
 
