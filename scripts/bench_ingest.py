@@ -77,11 +77,15 @@ def main():
         L.v2m_cuda_device_free(d)
 
     # through the C ABI with host buffers (H2D of the GT block inside), with overlap detection
-    t0 = time.perf_counter()
-    words, ov = v2m.paths_from_genotypes(gt, alt_offsets, edges_by_alt, h_pad, e_pad, ref_pos, edge_target_pos)
-    dt = time.perf_counter() - t0
-    assert np.array_equal(words, dev_words)
-    out["e2e"] = {"seconds": dt, "genotypes_per_s": R * H / dt, "h2d_bytes": int(gt.nbytes), "overlaps": int(len(ov))}
+    # (twice: the first call page-locks the two staging buffers, which the calling thread keeps afterwards)
+    times = []
+    for _ in range(2):
+        t0 = time.perf_counter()
+        words, ov = v2m.paths_from_genotypes(gt, alt_offsets, edges_by_alt, h_pad, e_pad, ref_pos, edge_target_pos)
+        times.append(time.perf_counter() - t0)
+        assert np.array_equal(words, dev_words)
+    dt = times[1]
+    out["e2e"] = {"seconds": dt, "first_call_seconds": times[0], "genotypes_per_s": R * H / dt, "h2d_bytes": int(gt.nbytes), "overlaps": int(len(ov))}
 
     if args.cpu_records:
         from oracle import oracle as orc

@@ -291,19 +291,34 @@ int paths_from_genotypes_device(unsigned short const *gt, u64 const n_records, u
 	// asynchronous copies, so that the host copy of block b + 1 overlaps the transfer and the kernels of block b.
 	cudaStream_t streams[2];
 	cudaEvent_t done[2];
-	unsigned short *h_gt[2] = {nullptr, nullptr};
+	// The two pinned staging buffers are kept per calling thread between calls: page-locking 2 × 64 MB costs more than
+	// sending them.
+	struct pinned_pair
+	{
+		unsigned short *h[2] = {nullptr, nullptr};
+		u64 bytes{};
+		~pinned_pair() { for (auto p : h) if (p) cudaFreeHost(p); }
+	};
+	thread_local pinned_pair staging;
+	unsigned short **h_gt(staging.h);
 	for (auto &s : streams) V2M_CUDA_TRY(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
 	for (auto &e : done) V2M_CUDA_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
 	struct guard_t
 	{
-		cudaStream_t *s; cudaEvent_t *e; unsigned short **h;
-		~guard_t() { for (int i(0); i < 2; ++i) { cudaStreamSynchronize(s[i]); cudaStreamDestroy(s[i]); cudaEventDestroy(e[i]); if (h[i]) cudaFreeHost(h[i]); } }
-	} const guard{streams, done, h_gt};
-	for (auto &h : h_gt)
-		if (cudaSuccess != cudaMallocHost(reinterpret_cast<void **>(&h), block_records * H * 2)) return fail(V2M_ERR_CUDA, "paths_from_genotypes: cudaMallocHost failed");
-	unsigned const copy_threads(std::max(1u, std::min(8u, std::thread::hardware_concurrency())));
+		cudaStream_t *s; cudaEvent_t *e;
+		~guard_t() { for (int i(0); i < 2; ++i) { cudaStreamSynchronize(s[i]); cudaStreamDestroy(s[i]); cudaEventDestroy(e[i]); } }
+	} const guard{streams, done};
+	if (staging.bytes < block_records * H * 2)
+	{
+		for (auto &h : staging.h) { if (h) cudaFreeHost(h); h = nullptr; }
+		staging.bytes = 0;
+		for (auto &h : staging.h)
+			if (cudaSuccess != cudaMallocHost(reinterpret_cast<void **>(&h), block_records * H * 2)) return fail(V2M_ERR_CUDA, "paths_from_genotypes: cudaMallocHost failed");
+		staging.bytes = block_records * H * 2;
+	}
+	unsigned const copy_threads(std::max(1u, std::min(16u, std::thread::hardware_concurrency())));
 	auto const stage([&](unsigned short *dst, unsigned short const *src, u64 const bytes) {
-		u64 const piece((bytes / copy_threads + 4095) & ~u64(4095));
+		u64 const piece(((bytes + copy_threads - 1) / copy_threads + 4095) & ~u64(4095));		// rounded up: never 0 for bytes > 0
 		std::vector<std::thread> pool;
 		for (unsigned t(1); t < copy_threads; ++t)
 			if (u64(t) * piece < bytes)
