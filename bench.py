@@ -105,6 +105,29 @@ class ClockSampler:
                 "source": "nvml" if self.nvml else "nvidia-smi"}
 
 
+# stdout carries the one JSON line and nothing else: the process's fd 1 is pointed at stderr for the whole run (NCCL prints
+# its version banner on fd 1 from C code when NCCL_DEBUG is set on the box), the line goes out through the saved descriptor.
+_JSON_FD = None
+
+
+def claim_stdout():
+    global _JSON_FD
+    if _JSON_FD is None:
+        sys.stdout.flush()
+        _JSON_FD = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit_line(line):
+    data = (json.dumps(line) + "\n").encode()
+    if _JSON_FD is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        sys.stdout.flush()
+        os.write(_JSON_FD, data)
+
+
 def dist_setup(n_gpus):
     rank, world, local = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
     dist = None
@@ -189,7 +212,7 @@ def cpu_reference_arm(args):
                          "sample": f"{n_rows} haplotype rows x {A} columns per step, row-parallel over {cores} threads, faithful I/O shape (4 KiB buffer, per-char gaps)"},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
-    print(json.dumps(line))
+    emit_line(line)
     return 0
 
 
@@ -211,6 +234,7 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()
+    claim_stdout()
     args.warmup = max(args.warmup, 3) if args.impl != "reference" else args.warmup
 
     if args.impl == "reference":
@@ -356,7 +380,7 @@ def main():
                        "sharding": "haplotype-row range per rank, no collective", "l2": "no flush needed: each step writes rows x A bytes (>> 126 MB L2) and re-reads < 1 GB"},
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks.summary(),
         }
-        print(json.dumps(line))
+        emit_line(line)
     if dist is not None:
         dist.destroy_process_group()
     return 0
