@@ -203,7 +203,9 @@ int v2m_cuda_last_cut_positions_timing(float *ms4, uint64_t *counts6);
  * Overlap reports (:405-418), optional (n_overlaps != NULL, record_ref_pos and edge_target_pos given): for every chromosome
  * copy, in record order, (record, row) is reported when record_ref_pos[r] < the target reference position of the copy's
  * previous ALT edge (edge_target_pos[edge], n_edges entries); pairs come back sorted by record, then row, i.e. in the
- * reference's reporting order. If overlap_cap is too small: V2M_ERR_ARGUMENT with the needed count in *n_overlaps. */
+ * reference's reporting order. If overlap_cap is too small: V2M_ERR_ARGUMENT with the needed count in *n_overlaps.
+ * gt may be pageable memory: it is staged in ~64 MB record blocks through two pinned buffers, which the calling thread keeps
+ * until it exits (so repeated calls, one per block of records, do not page-lock memory again). */
 int v2m_cuda_paths_from_genotypes(const uint16_t *gt, uint64_t n_records, uint32_t n_copies,
                                   const uint64_t *alt_offsets /* [n_records + 1] */, const uint64_t *edges_by_alt,
                                   const uint64_t *record_ref_pos, const uint64_t *edge_target_pos, uint64_t n_edges,

@@ -151,7 +151,10 @@ __device__ __forceinline__ u32 column_word(uint4 const (&v)[4], u32 const patter
 	return mine;
 }
 
-__global__ void __launch_bounds__(256)
+#ifndef V2M_K5_MIN_CTAS
+#define V2M_K5_MIN_CTAS 6		// 40 registers, 48 warps per SM: 0.371 -> 0.360 ms on 200k records x 5,008 copies (8: spills, 0.390 ms)
+#endif
+__global__ void __launch_bounds__(256, V2M_K5_MIN_CTAS)
 ingest_genotypes_kernel(unsigned short const * __restrict__ gt, u64 const n_records, u32 const H,
 	u64 const * __restrict__ alt_offsets, u64 const * __restrict__ edges_by_alt,
 	u32 const Wh32, u32 const blocks_per_record, u64 const e_pad, u32 * __restrict__ paths32, u32 * __restrict__ bad)
