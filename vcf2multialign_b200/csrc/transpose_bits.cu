@@ -38,6 +38,43 @@
 
 namespace v2m {
 
+// Cache-policy experiments (make VARIANT=… EXTRA=-DV2M_K1_LOAD_POLICY=1 …): 0 = plain __ldg / plain stores.
+#ifndef V2M_K1_LOAD_POLICY
+#define V2M_K1_LOAD_POLICY 0		// 1: L2 evict-first on the source (read once)
+#endif
+#ifndef V2M_K1_STORE_POLICY
+#define V2M_K1_STORE_POLICY 0		// 1: L2 evict-last on the destination (lines wait for the neighbouring tiles), 2: st.global.cs
+#endif
+
+__device__ __forceinline__ u64 k1_policy_evict_last()
+{
+	u64 policy;
+	asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(policy));
+	return policy;
+}
+
+__device__ __forceinline__ u64 k1_load(u64 const *p, u64 const policy)
+{
+#if V2M_K1_LOAD_POLICY == 1
+	u64 v;
+	asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.b64 %0, [%1], %2;" : "=l"(v) : "l"(p), "l"(policy));
+	return v;
+#else
+	return __ldg(p);
+#endif
+}
+
+__device__ __forceinline__ void k1_store(u32 *p, u32 const v, u64 const policy)
+{
+#if V2M_K1_STORE_POLICY == 1
+	asm volatile("st.global.L2::cache_hint.b32 [%0], %1, %2;" :: "l"(p), "r"(v), "l"(policy) : "memory");
+#elif V2M_K1_STORE_POLICY == 2
+	__stcs(p, v);
+#else
+	*p = v;
+#endif
+}
+
 constexpr int K1_TC = 512;			// source lines per tile
 constexpr int K1_TW = 32;			// 32-bit words per line per tile (1024 bits)
 constexpr int K1_THREADS = 512;
@@ -53,6 +90,7 @@ transpose_bits_kernel(u64 const * __restrict__ src, u32 * __restrict__ dst, u64 
 	u64 const c0(u64(blockIdx.y) * K1_TC);
 	u64 const p0(u64(blockIdx.x) * (K1_TW / 2));				// first 64-bit word (pair) of the row band
 	unsigned const tid(threadIdx.x);
+	[[maybe_unused]] u64 const ld_policy(V2M_K1_LOAD_POLICY ? l2_policy_evict_first() : 0), st_policy(1 == V2M_K1_STORE_POLICY ? k1_policy_evict_last() : 0);
 
 	// ---- load -------------------------------------------------------------------------------------------
 	{
@@ -64,7 +102,7 @@ transpose_bits_kernel(u64 const * __restrict__ src, u32 * __restrict__ dst, u64 
 		for (int p = 0; p < K1_TC / 32; ++p)
 		{
 			u64 const line(c0 + 32 * p + l_in_pass);
-			vals[p] = (pair_ok && line < C) ? __ldg(src + line * R64 + p0 + q) : 0;
+			vals[p] = (pair_ok && line < C) ? k1_load(src + line * R64 + p0 + q, ld_policy) : 0;
 		}
 #pragma unroll
 		for (int p = 0; p < K1_TC / 32; ++p)
@@ -99,7 +137,7 @@ transpose_bits_kernel(u64 const * __restrict__ src, u32 * __restrict__ dst, u64 
 		u32 *out(dst + r0 * C32 + xw);
 #pragma unroll
 		for (int j = 0; j < 32; ++j)
-			out[u64(j) * C32] = a[j];
+			k1_store(out + u64(j) * C32, a[j], st_policy);
 	}
 }
 
@@ -120,6 +158,7 @@ transpose_bits_tall_kernel(u64 const * __restrict__ src, u32 * __restrict__ dst,
 	u64 const c0(u64(blockIdx.y) * K1T_TC);
 	u64 const p0(u64(blockIdx.x) * (K1T_TW / 2));				// first 64-bit word (pair) of the row band
 	unsigned const tid(threadIdx.x);
+	[[maybe_unused]] u64 const ld_policy(V2M_K1_LOAD_POLICY ? l2_policy_evict_first() : 0), st_policy(1 == V2M_K1_STORE_POLICY ? k1_policy_evict_last() : 0);
 
 	{
 		unsigned const q(tid & 7);								// pair within the 64-byte piece of a line
@@ -130,7 +169,7 @@ transpose_bits_tall_kernel(u64 const * __restrict__ src, u32 * __restrict__ dst,
 		for (int p = 0; p < K1T_TC / 64; ++p)
 		{
 			u64 const line(c0 + 64 * p + l_in_pass);
-			vals[p] = (pair_ok && line < C) ? __ldg(src + line * R64 + p0 + q) : 0;
+			vals[p] = (pair_ok && line < C) ? k1_load(src + line * R64 + p0 + q, ld_policy) : 0;
 		}
 #pragma unroll
 		for (int p = 0; p < K1T_TC / 64; ++p)
@@ -162,7 +201,7 @@ transpose_bits_tall_kernel(u64 const * __restrict__ src, u32 * __restrict__ dst,
 		u32 *out(dst + r0 * C32 + xw);
 #pragma unroll
 		for (int j = 0; j < 32; ++j)
-			out[u64(j) * C32] = a[j];
+			k1_store(out + u64(j) * C32, a[j], st_policy);
 	}
 }
 
