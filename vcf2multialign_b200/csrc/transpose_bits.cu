@@ -38,12 +38,15 @@
 
 namespace v2m {
 
-// Cache-policy experiments (make VARIANT=… EXTRA=-DV2M_K1_LOAD_POLICY=1 …): 0 = plain __ldg / plain stores.
+// Cache policies (make VARIANT=… EXTRA=-DV2M_K1_LOAD_POLICY=1 …; 0 = plain __ldg / plain stores). Measured on c5 / 5056 ×
+// 1,155,008 (profiles/r01_transpose_cache_policy.txt): plain 1.609 / 0.331 ms; evict-last stores 1.567 / 0.324 ms (the
+// default: partially written destination lines stay in the L2 until the neighbouring tiles complete them); st.global.cs
+// 1.605 / 0.333 ms; evict-first, L1-no-allocate loads 2.018 / 0.400 ms (the bands' shared boundary sectors are lost).
 #ifndef V2M_K1_LOAD_POLICY
 #define V2M_K1_LOAD_POLICY 0		// 1: L2 evict-first on the source (read once)
 #endif
 #ifndef V2M_K1_STORE_POLICY
-#define V2M_K1_STORE_POLICY 0		// 1: L2 evict-last on the destination (lines wait for the neighbouring tiles), 2: st.global.cs
+#define V2M_K1_STORE_POLICY 1		// 1: L2 evict-last on the destination (lines wait for the neighbouring tiles), 2: st.global.cs
 #endif
 
 __device__ __forceinline__ u64 k1_policy_evict_last()
