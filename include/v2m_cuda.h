@@ -99,6 +99,8 @@ int v2m_cuda_graph_aligned_length(v2m_graph_t g, uint64_t *out);   /* aligned_po
 /* Copy-major path words as resident on the device (rows = e_pad, cols = h_pad): lets callers fetch the K1 result
  * when the view did not supply paths_by_chrom_copy_and_edge. */
 int v2m_cuda_graph_download_paths_by_chrom_copy_and_edge(v2m_graph_t g, uint64_t *dst);
+/* Lines [first_copy, first_copy + n_copies) of that matrix only (e_pad / 64 words per chromosome copy). */
+int v2m_cuda_graph_download_path_lines(v2m_graph_t g, uint32_t first_copy, uint32_t n_copies, uint64_t *dst);
 /* The REF-aligned template (= the bytes of the REF row), A bytes. */
 int v2m_cuda_graph_download_template(v2m_graph_t g, uint8_t *dst);
 
@@ -113,6 +115,10 @@ int v2m_cuda_plan_haplotypes(v2m_graph_t g, const uint32_t *copy_idx, uint32_t n
  * cut_positions has n_segments + 1 node ids, first 0, last the sink. */
 int v2m_cuda_plan_founders(v2m_graph_t g, const uint64_t *cut_positions, uint64_t n_segments,
                            const uint32_t *assigned, uint32_t n_founders, v2m_plan_t *out);
+/* Runs K2a again for every row of the plan, asynchronously on `stream` (NULL = default stream): the per-row edge test + jump
+ * of sequence_writer.cc:44-67 is part of every pass over the rows, so callers that time a whole pass (bench.py) put it inside
+ * the timed step; the plan's taken bits are rewritten with the same values. */
+int v2m_cuda_plan_resolve(v2m_plan_t p, void *stream);
 int v2m_cuda_plan_free(v2m_plan_t p);
 int v2m_cuda_plan_row_count(v2m_plan_t p, uint32_t *out);
 /* Taken-edge bits, one line of e_pad bits per row (bit e set iff the row's walk follows ALT edge e). */
@@ -234,6 +240,10 @@ int v2m_cuda_time_emit_rows(v2m_plan_t p, uint32_t row_begin, uint32_t row_end, 
  * counts4 = {chunks, cut positions, ALT edges, joined triples}. */
 int v2m_cuda_last_segment_classes_timing(float *ms3, uint64_t *counts4);
 int v2m_cuda_time_transpose_bits(const void *d_src, uint64_t rows, uint64_t cols, void *d_dst, int iters, float *ms_mean);
+/* The host link's ceiling for the end-to-end roofline: `iters` passes of plain cudaMemcpyAsync device-to-host copies of `bytes`
+ * in pieces of block_bytes, alternating between the calling thread's two streams (no kernel runs); *seconds = host time from
+ * the first copy to the last stream synchronisation. h_dst should be pinned (v2m_cuda_host_alloc). */
+int v2m_cuda_time_d2h_copies(void *h_dst, const void *d_src, uint64_t bytes, uint64_t block_bytes, int iters, double *seconds);
 /* K5 alone on GT values, offsets and edge indices already resident in HBM. */
 int v2m_cuda_time_ingest_genotypes(const void *d_gt, uint64_t n_records, uint32_t n_copies, const void *d_alt_offsets, const void *d_edges_by_alt,
                                    uint64_t h_pad, uint64_t e_pad, void *d_paths, int iters, float *ms_mean);

@@ -427,3 +427,49 @@ double orc_time_paths_loop(std::uint16_t const *gt, u64 n_records, u32 copies, u
 }
 
 } // extern "C"
+
+// ---- measurement infrastructure: CPU mirror of the synthetic path-bit generator (vcf2multialign_b200/csrc/synth.cu,
+// synth.py:allele_numpy) — not a restatement of the reference. bench.py's CPU legs use it to make the copy-major path
+// lines of a few sampled chromosome copies of the big shapes without touching the GPU library.
+namespace {
+	inline u32 synth_hash32(u32 x) { x ^= x >> 16; x *= 0x7feb352du; x ^= x >> 15; x *= 0x846ca68bu; x ^= x >> 16; return x; }
+	inline u32 synth_mix(u32 seed, u32 a, u32 b) { return synth_hash32(synth_hash32(a ^ seed) + b); }
+	inline u32 synth_allele(u32 seed, u32 h, u32 site, u32 n_alts, u32 thr)
+	{
+		u32 const off(synth_mix(seed, h, 23) & 8191u);
+		u32 const block((site + off) >> 13);
+		u32 const founder(synth_mix(seed, h * 0x9e3779b1u + block, 37) & 63u);
+		u32 const fh(synth_mix(seed, site * 64u + founder, 41));
+		bool const nonref((fh & 0xffffu) < thr);
+		u32 alt(n_alts > 1 ? (fh >> 16) & 1u : 0u);
+		bool const mut(0 == (synth_mix(seed, h * 0x85ebca6bu + site, 53) & 1023u));
+		if (mut && !nonref) alt = 0;
+		return (nonref != mut) ? alt + 1 : 0;
+	}
+}
+
+extern "C" void orc_synth_path_lines(u32 seed, u32 first_copy, u32 n_copies, u64 E, u64 We, u32 const *edge_site, std::uint8_t const *edge_alt,
+	std::uint8_t const *edge_nalts, u64 *dst /* n_copies x We words, copy-major lines */, int threads)
+{
+	std::fill(dst, dst + u64(n_copies) * We, u64(0));
+	std::atomic<u32> next(0);
+	auto worker([&]{
+		while (true)
+		{
+			u32 const i(next.fetch_add(1));
+			if (i >= n_copies) break;
+			u32 const h(first_copy + i);
+			u64 *line(dst + u64(i) * We);
+			for (u64 e(0); e < E; ++e)
+			{
+				u32 const site(edge_site[e]);
+				u32 const thr(65536u >> (2u + synth_mix(seed, site, 11) % 10u));
+				if (1u + edge_alt[e] == synth_allele(seed, h, site, edge_nalts[e], thr)) line[e / 64] |= u64(1) << (e % 64);
+			}
+		}
+	});
+	std::vector<std::thread> pool;
+	for (int t(1); t < threads; ++t) pool.emplace_back(worker);
+	worker();
+	for (auto &t : pool) t.join();
+}

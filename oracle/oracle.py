@@ -86,6 +86,8 @@ def lib():
     L.orc_time_rows.argtypes = [vp, u32, u32, i32, i32, vp]
     L.orc_time_transpose.restype = C.c_double
     L.orc_time_transpose.argtypes = [vp, u64, u64, vp]
+    L.orc_synth_path_lines.restype = None
+    L.orc_synth_path_lines.argtypes = [u32, u32, u32, u64, u64, vp, vp, vp, vp, i32]
     _lib = L
     return L
 
@@ -139,6 +141,17 @@ def transpose(words: np.ndarray, rows: int, cols: int) -> np.ndarray:
     if lib().orc_transpose(_ptr(words), rows, cols, _ptr(dst)):
         raise _err()
     return dst
+
+
+def synth_path_lines(seed: int, first_copy: int, n_copies: int, e_pad: int, edge_site, edge_alt, edge_nalts, threads: int = 1) -> np.ndarray:
+    """Measurement infrastructure (not the reference's algorithm): copy-major path lines of the synthetic workloads for a few
+    chromosome copies, the CPU mirror of vcf2multialign_b200/csrc/synth.cu."""
+    site = np.ascontiguousarray(edge_site, np.uint32)
+    alt = np.ascontiguousarray(edge_alt, np.uint8)
+    nalts = np.ascontiguousarray(edge_nalts, np.uint8)
+    out = np.zeros(max(n_copies * (e_pad // 64), 1), np.uint64)
+    lib().orc_synth_path_lines(seed & 0xFFFFFFFF, first_copy, n_copies, site.size, e_pad // 64, _ptr(site), _ptr(alt), _ptr(nalts), _ptr(out), threads)
+    return out[: n_copies * (e_pad // 64)]
 
 
 def transpose8x8(word: int, terms: bool = False) -> int:

@@ -217,6 +217,49 @@ def test_rows_dense_tiles_fall_back_to_global_arrays(v2m, tmp_path):
             assert win[i].tobytes() == full[r][c0:c1], (r, c0, c1)
 
 
+def test_rows_windows_under_16_bytes_in_last_tile(v2m):
+    """Rows whose window leaves fewer than 16 bytes in its last 4096-column tile hand the TMA engine nothing for that tile
+    (the bytes go out lane by lane). With more units than SMs, so that CTAs draw several units, and more than two rows per
+    row warp in the last-tile unit, the row buffers are reused right after such rows: their reuse must still wait for the
+    bulk store that last read them (emit_rows commits one bulk group per row, empty or not)."""
+    from vcf2multialign_b200 import synth
+    w = synth.make_workload("tail", seed=5, ref_len=700_000, n_sites=4000, n_samples=32, with_paths=True)
+    g = w.graph
+    for tail in (1, 7, 15):
+        # move the sink so that A % 4096 == tail: the last node only ends the reference, nothing else refers to its position
+        A0 = int(g.aligned_positions[-1])
+        d = (tail - A0) % 4096
+        ref = np.concatenate([w.ref, synth.BASES[np.arange(d) % 4]])
+        g.reference_positions = g.reference_positions.copy(); g.reference_positions[-1] += np.uint64(d)
+        g.aligned_positions = g.aligned_positions.copy(); g.aligned_positions[-1] += np.uint64(d)
+        A = int(g.aligned_positions[-1])
+        assert A % 4096 == tail and A // 4096 > 160
+        ec = g.paths_by_edge_and_chrom_copy
+        og = orc.Graph.from_arrays(dict(
+            reference_positions=g.reference_positions, aligned_positions=g.aligned_positions, alt_edge_targets=g.alt_edge_targets,
+            alt_edge_count_csum=g.alt_edge_count_csum, label_offsets=g.label_offsets, label_chars=g.label_chars,
+            paths_ec=ec, paths_ce=orc.transpose(ec, g.h_pad, g.e_pad), h_pad=g.h_pad, e_pad=g.e_pad, ploidy_csum=g.ploidy_csum,
+            sample_names=g.sample_names, ref=ref))
+        dg = v2m.DeviceGraph(g, ref)
+        H = g.total_chromosome_copies()
+        idx = [orc.PLOIDY_MAX] + list(range(H))                 # 65 rows: two row chunks, up to 4 rows per row warp
+        plan = dg.plan_haplotypes(idx)
+        full = [og.output_sequence(h) for h in idx]
+        for _ in range(3):                                      # the hazard is a race: give it more than one chance
+            rows = plan.emit_rows()
+            for i in range(len(idx)):
+                assert rows[i].tobytes() == full[i], (tail, i)
+        # column windows that end 1 … 15 bytes into a tile, starting in the tile before (or further back)
+        for c1 in (4096 * 100 + 3, 4096 * 161 + 15, 4096 * 37 + 9):
+            for c0 in (c1 - 5000, 0):
+                win = plan.emit_rows(0, len(idx), c0, c1)
+                for i in range(len(idx)):
+                    assert win[i].tobytes() == full[i][c0:c1], (tail, i, c0, c1)
+        plan.close()
+        dg.close()
+        w.ref = ref
+
+
 def test_founder_rows_random(v2m, tmp_path):
     """Founder rows given the oracle's cut positions and matchings (K2c = compose + K2a + K2b)."""
     done = 0

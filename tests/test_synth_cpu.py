@@ -42,3 +42,18 @@ def test_workload_statistics():
     window = bits[:64].T
     assert len({r.tobytes() for r in window}) < H
     assert int(g.aligned_positions[-1]) > int(g.reference_positions[-1])
+
+
+def test_cpu_mirror_of_the_path_bit_generator():
+    """bench.py's CPU legs make the path lines of sampled chromosome copies with oracle.synth_path_lines (C++ mirror of
+    csrc/synth.cu); it must agree with the numpy model the small shapes are built with."""
+    from oracle import oracle as orc
+    w = synth.make_workload("small", seed=4, with_paths=True)
+    g = w.graph
+    H, We = g.total_chromosome_copies(), g.e_pad // 64
+    n_alts = np.bincount(w.edge_site, minlength=len(w.site_pos)).astype(np.uint8)
+    ce = orc.transpose(g.paths_by_edge_and_chrom_copy, g.h_pad, g.e_pad)
+    got = orc.synth_path_lines(w.seed, 0, H, g.e_pad, w.edge_site, w.edge_alt, n_alts[w.edge_site], threads=3)
+    assert np.array_equal(got, ce[: H * We])
+    part = orc.synth_path_lines(w.seed, 7, 5, g.e_pad, w.edge_site, w.edge_alt, n_alts[w.edge_site], threads=1)
+    assert np.array_equal(part, ce[7 * We : 12 * We])

@@ -64,9 +64,11 @@ SYMBOLS = {
     "v2m_cuda_graph_free": (_i32, [_vp]),
     "v2m_cuda_graph_aligned_length": (_i32, [_vp, _vp]),
     "v2m_cuda_graph_download_paths_by_chrom_copy_and_edge": (_i32, [_vp, _vp]),
+    "v2m_cuda_graph_download_path_lines": (_i32, [_vp, _u32, _u32, _vp]),
     "v2m_cuda_graph_download_template": (_i32, [_vp, _vp]),
     "v2m_cuda_plan_haplotypes": (_i32, [_vp, _vp, _u32, _vp]),
     "v2m_cuda_plan_founders": (_i32, [_vp, _vp, _u64, _vp, _u32, _vp]),
+    "v2m_cuda_plan_resolve": (_i32, [_vp, _vp]),
     "v2m_cuda_plan_free": (_i32, [_vp]),
     "v2m_cuda_plan_row_count": (_i32, [_vp, _vp]),
     "v2m_cuda_plan_download_taken": (_i32, [_vp, _vp]),
@@ -88,6 +90,7 @@ SYMBOLS = {
     "v2m_cuda_synth_paths": (_i32, [_vp, _u64, _u64, _u32, _u64, _u32, _vp, _vp, _vp]),
     "v2m_cuda_time_emit_rows": (_i32, [_vp, _u32, _u32, _vp, _u64, _i32, _vp]),
     "v2m_cuda_time_transpose_bits": (_i32, [_vp, _u64, _u64, _vp, _i32, _vp]),
+    "v2m_cuda_time_d2h_copies": (_i32, [_vp, _vp, _u64, _u64, _i32, _vp]),
 }
 
 _lib = None

@@ -3,6 +3,7 @@
 #include <algorithm>
 #include <atomic>
 #include <cerrno>
+#include <chrono>
 #include <cstring>
 #include <memory>
 #include <string>
@@ -61,7 +62,7 @@ namespace v2m {
 		graph_holder const		*owner{};
 		std::vector<u64>		unaligned_lengths;	// host copy of p.lengths once computed
 
-		~plan_holder() { cudaFree(p.taken); cudaFree(p.prefix); cudaFree(p.lengths); }
+		~plan_holder() { cudaFree(p.taken); cudaFree(p.prefix); cudaFree(p.lengths); cudaFree(p.line_idx); cudaFree(p.own_lines); }
 	};
 }
 
@@ -316,6 +317,15 @@ int v2m_cuda_graph_download_paths_by_chrom_copy_and_edge(v2m_graph_t g, uint64_t
 	return V2M_OK;
 }
 
+int v2m_cuda_graph_download_path_lines(v2m_graph_t g, uint32_t first_copy, uint32_t n_copies, uint64_t *dst)
+{
+	if (!g || (!dst && n_copies)) return fail(V2M_ERR_ARGUMENT, "NULL argument");
+	if (u64(first_copy) + n_copies > g->g.h_pad) return fail(V2M_ERR_ARGUMENT, "graph_download_path_lines: chromosome copy range out of bounds");
+	if (n_copies && g->g.We)
+		V2M_CUDA_TRY(cudaMemcpy(dst, g->g.paths_he + u64(first_copy) * g->g.We, u64(n_copies) * g->g.We * 8, cudaMemcpyDeviceToHost));
+	return V2M_OK;
+}
+
 int v2m_cuda_graph_download_template(v2m_graph_t g, uint8_t *dst)
 {
 	if (!g || !dst) return fail(V2M_ERR_ARGUMENT, "NULL argument");
@@ -337,11 +347,10 @@ int v2m_cuda_plan_haplotypes(v2m_graph_t g, const uint32_t *copy_idx, uint32_t n
 	holder->p.graph = &g->g;
 	holder->p.n_rows = n_rows;
 	if (int const st = dev_alloc(holder->p.taken, u64(n_rows) * g->g.We)) return st;
-	u32 *d_idx(nullptr);
-	if (int const st = dev_upload(d_idx, copy_idx, n_rows)) return st;
-	int const st(launch_resolve_rows(g->g, g->g.paths_he, d_idx, n_rows, holder->p.taken, nullptr));
+	if (int const st = dev_upload(holder->p.line_idx, copy_idx, n_rows)) return st;
+	holder->p.lines = g->g.paths_he;
+	int const st(launch_resolve_rows(g->g, holder->p.lines, holder->p.line_idx, n_rows, holder->p.taken, nullptr));
 	cudaError_t const err(cudaDeviceSynchronize());
-	cudaFree(d_idx);
 	if (st) return st;
 	if (cudaSuccess != err) return fail(V2M_ERR_CUDA, std::string("resolve_rows: ") + cudaGetErrorString(err));
 	*out = holder.release();
@@ -386,10 +395,18 @@ int v2m_cuda_plan_founders(v2m_graph_t g, const uint64_t *cut_positions, uint64_
 		cudaError_t const err(cudaDeviceSynchronize());
 		if (cudaSuccess != err) st = fail(V2M_ERR_CUDA, std::string("plan_founders: ") + cudaGetErrorString(err));
 	} while (false);
-	cudaFree(d_cut_edges); cudaFree(d_assigned); cudaFree(d_lines);
-	if (st) return st;
+	cudaFree(d_cut_edges); cudaFree(d_assigned);
+	if (st) { cudaFree(d_lines); return st; }
+	holder->p.own_lines = d_lines;
+	holder->p.lines = d_lines;
 	*out = holder.release();
 	return V2M_OK;
+}
+
+int v2m_cuda_plan_resolve(v2m_plan_t p, void *stream)
+{
+	if (!p) return fail(V2M_ERR_ARGUMENT, "plan_resolve: NULL plan");
+	return launch_resolve_rows(*p->p.graph, p->p.lines, p->p.line_idx, p->p.n_rows, p->p.taken, static_cast<cudaStream_t>(stream));
 }
 
 int v2m_cuda_plan_free(v2m_plan_t p)
@@ -594,6 +611,23 @@ int v2m_cuda_emit_rows_unaligned(v2m_plan_t p, uint32_t row_begin, uint32_t row_
 	} while (false);
 	cudaFree(d_out); cudaFree(d_offsets);
 	return st;
+}
+
+// Plain D2H copies, no kernel: the host link's ceiling for the end-to-end roofline (bench.py e2e.peak, scripts/microbench).
+int v2m_cuda_time_d2h_copies(void *h_dst, const void *d_src, uint64_t bytes, uint64_t block_bytes, int iters, double *seconds)
+{
+	if (!h_dst || !d_src || !seconds || 0 == bytes || 0 == block_bytes || iters < 1) return fail(V2M_ERR_ARGUMENT, "time_d2h_copies: bad argument");
+	staging_area &sa(thread_staging());
+	if (int const st = sa.reserve(0)) return st;
+	V2M_CUDA_TRY(cudaDeviceSynchronize());
+	auto const t0(std::chrono::steady_clock::now());
+	int k(0);
+	for (int it(0); it < iters; ++it)
+		for (u64 off(0); off < bytes; off += block_bytes, k ^= 1)
+			V2M_CUDA_TRY(cudaMemcpyAsync(static_cast<u8 *>(h_dst) + off, static_cast<u8 const *>(d_src) + off, std::min(block_bytes, bytes - off), cudaMemcpyDeviceToHost, sa.streams[k]));
+	for (int i(0); i < 2; ++i) V2M_CUDA_TRY(cudaStreamSynchronize(sa.streams[i]));
+	*seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+	return V2M_OK;
 }
 
 int v2m_cuda_time_emit_rows(v2m_plan_t p, uint32_t row_begin, uint32_t row_end, void *d_out, uint64_t pitch, int iters, float *ms_mean)

@@ -64,6 +64,9 @@ struct device_plan
 	device_graph const	*graph{};
 	u32					n_rows{};
 	u64					*taken{};			// n_rows × We
+	u64 const			*lines{};			// K2a input: We-word path lines (the graph's paths_he, or the composed founder lines below)
+	u32					*line_idx{};		// haplotype plans: row i reads line line_idx[i] (PLOIDY_MAX: the REF row); founders: NULL
+	u64					*own_lines{};		// founder plans: n_rows composed lines (compose_founder_kernel)
 	int					*prefix{};			// --unaligned: n_rows × (We + 1) exclusive prefix sums of (|label| − REF span) over taken edges
 	u64					*lengths{};			// --unaligned: n_rows row lengths
 };

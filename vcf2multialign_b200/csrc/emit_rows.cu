@@ -211,7 +211,7 @@ resolve_rows_kernel(u64 const * __restrict__ lines, u32 const * __restrict__ lin
 //   units   the launch is cut into units of one tile of K2_TCOL aligned columns × rows_per_unit (<= K2P_UNIT_ROWS) rows,
 //           numbered tile-fastest. CTAs draw unit numbers from a ticket counter, so an SM that is served more slowly by
 //           the memory system simply takes fewer units (with a fixed assignment single SMs ran 20 % longer than the
-//           rest); the last CTA to find the counter exhausted zeroes it for the next launch on the stream.
+//           rest); the counter is zeroed on the stream before each launch.
 //   stage   per unit the staging warp (a) has one lane issue three bulk async copies (TMA engine) global → shared: the
 //           tile of the REF template, the records of the ALT edges that can intersect the tile and those edges' label
 //           bytes (contiguous in the flattened label store), so that patching never leaves the SM; (b) gathers the
@@ -279,7 +279,7 @@ struct emit_params
 	u64				first_tile;			// col_begin / K2_TCOL
 	u32				n_tiles;			// tiles the column window touches
 	u32				rows_per_unit, n_row_chunks;
-	u32				*tickets;			// [0] next unit, [1] CTAs that ran out of units; both 0 between launches
+	u32				*tickets;			// [0] next unit; zeroed on the launch stream before every launch
 	u8				*out;
 	u64				pitch;
 };
@@ -374,13 +374,6 @@ emit_rows_kernel(emit_params const p)
 			if (0 == lane) mbar_arrive(&sm.full[s]);		// release: the header and the words are visible to the waiters
 			unit = unit_after;
 			te = te_after;
-		}
-		if (0 != lane) return;
-		// The last CTA to run out of units leaves the tickets as it found them, for the next launch on this stream.
-		if (atomicAdd(p.tickets + 1, 1u) == gridDim.x - 1)
-		{
-			p.tickets[0] = 0;
-			p.tickets[1] = 0;
 		}
 		return;
 	}
@@ -531,9 +524,12 @@ emit_rows_kernel(emit_params const p)
 					fence_proxy_async_smem();
 					__syncwarp();
 					u8 *orow(p.out + u64(r - p.row_begin) * p.pitch + (c0 - p.col_begin));
-					if (0 == lane && bulk_bytes)
+					if (0 == lane)
 					{
-						bulk_s2g_hint(orow, buf + off0, bulk_bytes, store_policy);
+						// One bulk group per row, empty when the row's window is under 16 bytes: n_issued picks the buffer and
+						// wait_group.read<1> counts groups, so the two must advance together (otherwise two such rows in a row
+						// would let the second one refill a buffer the engine may still be reading).
+						if (bulk_bytes) bulk_s2g_hint(orow, buf + off0, bulk_bytes, store_policy);
 						bulk_commit();
 					}
 					if (lane < n_bytes - bulk_bytes)
@@ -582,9 +578,9 @@ int launch_resolve_rows(device_graph const &g, u64 const *d_lines, u32 const *d_
 	return 0;
 }
 
-// The unit tickets of emit_rows_kernel: one pair per (device, stream). Launches on one stream run one after the other and
-// each leaves its pair zeroed, so the pair needs no host-side reset; cudaStreamPerThread names a different stream in every
-// host thread, hence the thread id in the key.
+// The unit ticket of emit_rows_kernel: one counter per (device, stream), zeroed by an 8-byte memset on the launch stream
+// before every launch (so an aborted launch cannot poison the next one on the same or a recycled stream handle);
+// cudaStreamPerThread names a different stream in every host thread, hence the thread id in the key.
 static int unit_tickets(int const dev, cudaStream_t const stream, u32 *&tickets)
 {
 	static std::mutex mtx;
@@ -592,11 +588,9 @@ static int unit_tickets(int const dev, cudaStream_t const stream, u32 *&tickets)
 	std::lock_guard<std::mutex> const lock(mtx);
 	u32 *&slot(table[{dev, stream, cudaStreamPerThread == stream ? std::this_thread::get_id() : std::thread::id()}]);
 	if (!slot)
-	{
 		V2M_CUDA_TRY(cudaMalloc(&slot, 2 * sizeof(u32)));
-		V2M_CUDA_TRY(cudaMemsetAsync(slot, 0, 2 * sizeof(u32), stream));
-	}
 	tickets = slot;
+	V2M_CUDA_TRY(cudaMemsetAsync(slot, 0, 2 * sizeof(u32), stream));
 	return 0;
 }
 
