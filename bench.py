@@ -337,9 +337,7 @@ def main():
     rows_idx = np.ascontiguousarray(rows_all[row_begin:row_end])
     plan = dgraph.plan_haplotypes(rows_idx)
     n_rows = int(rows_idx.size)
-    pitch = (A + 127) // 128 * 128      # rows of the device ring start on a 128-byte line (as the library's own buffers do)
-    if pitch % 4096 == 0:
-        pitch += 128
+    pitch = int(L.v2m_cuda_row_pitch(A))      # rows start on a 128-byte line, as in the library's own buffers
     max_block = args.block_rows if args.block_rows > 0 else min(512, max(64, (32 << 30) // pitch // 64 * 64))
     n_launches = max(1, (n_rows + max_block - 1) // max_block)
     block = (n_rows + n_launches - 1) // n_launches            # launches sized to the shard: no short tail launch
@@ -438,9 +436,20 @@ def main():
                   + g.alt_edge_count_csum.nbytes + g.label_offsets.nbytes + len(g.label_chars) + rows_idx.nbytes)
         d2h = int(n_rows * A)
 
+        shard = args.scaling == "strong" and world > 1
+        copies = rows_idx[rows_idx != v2m.PLOIDY_MAX]
+        if shard:
+            h2d -= int(paths_ec.nbytes) - int(g.e_pad * ((int(copies.max()) + 64) // 64 - int(copies.min()) // 64) * 8)
+
         def e2e_step(row_limit=None):
-            dg = v2m.DeviceGraph(g, w.ref)                       # H2D of the graph + K1 transpose + template
-            pl = dg.plan_haplotypes(rows_idx)                     # K2a
+            if shard:
+                # this rank's slab of the path matrix only (cut out of the host matrix inside the timed step)
+                sg, off = sharding.shard_graph(g, int(copies.min()), int(copies.max()) + 1)
+                local_idx = np.where(rows_idx == v2m.PLOIDY_MAX, rows_idx, rows_idx - np.uint32(off)).astype(np.uint32)
+            else:
+                sg, local_idx = g, rows_idx
+            dg = v2m.DeviceGraph(sg, w.ref)                       # H2D of the graph + K1 transpose + template
+            pl = dg.plan_haplotypes(local_idx)                    # K2a
             for r0 in range(0, row_limit or n_rows, e2e_block):   # K2b → pinned host
                 check(L.v2m_cuda_emit_rows(pl._p, r0, min(n_rows, r0 + e2e_block), 0, A, h_out, pitch))
             pl.close()
@@ -470,7 +479,7 @@ def main():
                "peak": link_peak, "peak_unit": "GB/s", "frac": e2e_value / link_peak,
                "peak_source": f"measured live on this box: plain cudaMemcpyAsync D2H into pinned memory, {copy_bytes} B per pass in 256 MiB pieces on two streams, "
                               f"{iters} passes, all {world} rank(s) copying at once (sum over ranks / slowest rank); 1 byte crosses the link per base",
-               "note": "graph upload (host arrays) + K1 + K2a + K2b with this rank's rows copied into pinned host memory; full job per step; byte counts are per rank"}
+               "note": "graph upload (host arrays" + ("; this rank's slab of the path matrix, sharding.shard_graph" if shard else "") + ") + K1 + K2a + K2b with this rank's rows copied into pinned host memory; full job per step; byte counts are per rank"}
         L.v2m_cuda_host_free(h_out)
         g.paths_by_edge_and_chrom_copy = None
 

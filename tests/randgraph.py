@@ -128,3 +128,31 @@ def model_row(a, taken, template=None):
         label = ch[int(off[e]) : int(off[e + 1])]
         row[a0:a1] = label + b"-" * (a1 - a0 - len(label))
     return bytes(row)
+
+
+def model_simple_edges(a):
+    """K2a's static property: edge e is simple iff no earlier edge's target node lies beyond src(e); a simple edge is taken
+    whenever its path bit is set."""
+    csum = a["alt_edge_count_csum"]
+    src = np.repeat(np.arange(len(csum) - 1), np.diff(csum).astype(np.int64))
+    tgt = np.asarray(a["alt_edge_targets"], np.int64)
+    reach = np.concatenate([[0], np.maximum.accumulate(tgt)[:-1]]) if len(tgt) else np.zeros(0, np.int64)
+    return reach <= src
+
+
+def model_taken_edges_with_simple_mask(a, h, group=32 * 64):
+    """The walk as resolve_rows_kernel runs it: simple set edges are taken outright; a set non-simple edge is compared with the
+    target of the last taken edge (the taken edge with the largest index)."""
+    E = len(a["alt_edge_targets"])
+    We = a["e_pad"] // 64
+    csum = a["alt_edge_count_csum"]
+    src = np.repeat(np.arange(len(csum) - 1), np.diff(csum).astype(np.int64))
+    simple = model_simple_edges(a)
+    taken, last = [], -1
+    for e in range(E):
+        if not bit(a["paths_ce"], We, h, e):
+            continue
+        if simple[e] or src[e] >= (int(a["alt_edge_targets"][last]) if last >= 0 else 0):
+            taken.append(e)
+            last = e
+    return taken

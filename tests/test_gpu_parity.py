@@ -803,3 +803,26 @@ def test_sharded_stream_gpu_rows(v2m, tmp_path, unaligned):
     for rank in range(world):
         sharding.sharded_haplotype_output_a2m(out, g, dg, dst, rank, world, dist, block_rows=4)
     assert open(dst, "rb").read() == og.haplotype_output_a2m("c", True, unaligned)
+
+
+def test_shard_graph_rows_on_device(v2m, tmp_path):
+    """A rank's slab of the path matrix (sharding.shard_graph) uploaded on its own gives that rank's rows of the cohort."""
+    from vcf2multialign_b200 import sharding
+    og = rg.random_oracle_graph(str(tmp_path), 99, ref_len=9000, n_records=800, n_samples=90, ploidy=2, long_del_prob=0.03)
+    a = dict(og.arrays())
+    a["paths_ce"] = None
+    g = v2m.VariantGraph.from_arrays(a)
+    H = g.total_chromosome_copies()
+    for world in (2, 3):
+        for rank in range(world):
+            b, e = sharding.row_range(H + 1, rank, world)                     # rows: REF, then every copy
+            rows = [orc.PLOIDY_MAX if r == 0 else r - 1 for r in range(b, e)]
+            copies = [c for c in rows if c != orc.PLOIDY_MAX]
+            sub, off = sharding.shard_graph(g, min(copies), max(copies) + 1)
+            dg = v2m.DeviceGraph(sub, og.arrays()["ref"])
+            plan = dg.plan_haplotypes([c if c == orc.PLOIDY_MAX else c - off for c in rows])
+            out = plan.emit_rows()
+            for i, c in enumerate(rows):
+                assert out[i].tobytes() == og.output_sequence(c), (world, rank, c)
+            plan.close()
+            dg.close()

@@ -26,3 +26,15 @@ def test_overlaps_are_exercised(tmp_path):
         g = rg.random_oracle_graph(str(tmp_path), seed, ref_len=150 + 7 * seed, n_records=10 + seed, n_samples=4, ploidy=1 + seed % 3)
         n += len(g.overlaps())
     assert n > 20
+
+
+@pytest.mark.parametrize("seed", range(30))
+def test_simple_edges_need_no_walk_state(tmp_path, seed):
+    """K2a (resolve_rows_kernel) decides set bits of 'simple' edges without loading anything: check the rule against the walk."""
+    g = rg.random_oracle_graph(str(tmp_path), 100 + seed, ref_len=200 + 9 * seed, n_records=20 + 2 * seed, n_samples=5,
+                               ploidy=1 + seed % 2, long_del_prob=0.08 if seed % 2 else 0.0, many_alts_prob=0.2 if seed % 3 == 0 else 0.0)
+    a = g.arrays()
+    simple = rg.model_simple_edges(a)
+    assert simple.any() and (not simple.all() or seed % 2 == 0)
+    for h in range(a["total_copies"]):
+        assert rg.model_taken_edges_with_simple_mask(a, h) == rg.model_taken_edges(a, h), (seed, h)

@@ -106,3 +106,29 @@ def test_single_process_stream(tmp_path):
     dst = str(tmp_path / "single.a2m")
     sharding.sharded_haplotype_output_a2m(out, g, None, dst, row_source=OracleRows(og))
     assert open(dst, "rb").read() == og.haplotype_output_a2m(None, True, False)
+
+
+def test_shard_graph_rows_equal_cohort_rows():
+    """sharding.shard_graph: a rank's slab of the path matrices gives the same rows (checked with the oracle's row writer)."""
+    import numpy as np
+    from oracle import oracle as orc
+    from vcf2multialign_b200 import sharding, synth
+    w = synth.make_workload("x", seed=11, ref_len=30_000, n_sites=900, n_samples=100, with_paths=True)
+    g = w.graph
+    g.paths_by_chrom_copy_and_edge = orc.transpose(g.paths_by_edge_and_chrom_copy, g.h_pad, g.e_pad)
+
+    def oracle_graph(vg):
+        return orc.Graph.from_arrays(dict(
+            reference_positions=vg.reference_positions, aligned_positions=vg.aligned_positions, alt_edge_targets=vg.alt_edge_targets,
+            alt_edge_count_csum=vg.alt_edge_count_csum, label_offsets=vg.label_offsets, label_chars=vg.label_chars,
+            paths_ec=vg.paths_by_edge_and_chrom_copy, paths_ce=vg.paths_by_chrom_copy_and_edge, h_pad=vg.h_pad, e_pad=vg.e_pad,
+            ploidy_csum=vg.ploidy_csum, sample_names=vg.sample_names, ref=w.ref))
+
+    full = oracle_graph(g)
+    for begin, end in ((0, 200), (70, 131), (128, 192), (199, 200), (63, 65)):
+        sub, off = sharding.shard_graph(g, begin, end)
+        assert off % 64 == 0 and off <= begin and sub.h_pad % 64 == 0 and sub.h_pad <= g.h_pad
+        assert np.array_equal(sub.paths_by_chrom_copy_and_edge, orc.transpose(sub.paths_by_edge_and_chrom_copy, sub.h_pad, sub.e_pad))
+        og = oracle_graph(sub)
+        for c in {begin, (begin + end) // 2, end - 1}:
+            assert og.output_sequence(c - off) == full.output_sequence(c), (begin, end, c)

@@ -76,6 +76,7 @@ SYMBOLS = {
     "v2m_cuda_emit_rows_device": (_i32, [_vp, _u32, _u32, _u64, _u64, _vp, _u64, _vp]),
     "v2m_cuda_emit_rows": (_i32, [_vp, _u32, _u32, _u64, _u64, _vp, _u64]),
     "v2m_cuda_release_staging": (None, []),
+    "v2m_cuda_row_pitch": (_u64, [_u64]),
     "v2m_cuda_emit_rows_unaligned": (_i32, [_vp, _u32, _u32, _vp, _vp]),
     "v2m_cuda_write_a2m": (_i32, [_vp, C.c_char_p, _i32, _i32, ROW_CALLBACK, _vp]),
     "v2m_cuda_stream_a2m": (_i32, [_vp, C.c_char_p, _i32, SINK, _vp, ROW_CALLBACK, _vp]),

@@ -14,7 +14,8 @@
 //   build_template_kernel   REF-aligned template, A bytes, once per graph.
 //   compose_founder_kernel  path bits of founder rows: per segment the bits of the assigned chromosome copy
 //                           (founder_sequence_writing_delegate::handle_node, founder_…cc:106-114).
-//   resolve_rows_kernel     K2a: path bits → taken bits, one warp per row, 2048 edges per step.
+//   resolve_rows_kernel     K2a: path bits → taken bits, one warp per row, 8192 edges per step; per-edge loads only for set
+//                           bits of edges that an earlier edge can reach over.
 //   emit_rows_kernel        K2b: rows × columns tile writer, persistent CTAs; template tile + edge records staged in shared
 //                           memory by bulk async copies one tile ahead, rows assembled in shared memory and written by
 //                           the TMA engine.
@@ -121,33 +122,22 @@ compose_founder_kernel(u64 const * __restrict__ paths_he, u64 const We,
 // ---------------------------------------------------------------------------------------------------------
 // K2a resolve_rows: path bits → taken bits
 // ---------------------------------------------------------------------------------------------------------
-struct word_result { u64 taken; u32 cur_out; u32 s_first; };
+// The walk takes set edge e iff src(e) >= target of the last taken edge (sequence_writer.cc:51-67; targets of taken edges
+// grow along the walk, so "the last taken edge" is the taken edge with the largest index). Most edges can be decided without
+// looking at the walk at all: edge e is *simple* when no earlier edge of the graph — set or not — reaches beyond its source
+// node (max over e' < e of tgt(e') <= src(e): true for every first ALT of a site that no earlier deletion spans), and a simple
+// edge is taken whenever its bit is set. graph_upload stores that property as one bit per edge (edge_simple, E_pad / 8 bytes,
+// L2-resident), so the common case is `taken = path word` with no per-edge load; only set bits of non-simple edges (second
+// ALTs of multi-allelic sites, edges under an overlapping deletion) are resolved by the walk's rule, in order, with the
+// target of the last taken edge fetched when one of them needs it. The first version loaded edge_src / edge_tgt for every
+// set bit: ~1.9 G scattered 4-byte loads on c4, bound by L2 sector throughput at 520 GB/s of algorithmic traffic.
+// One warp per output row, K2A_UNROLL × 32 words (8192 edges at 4) per step with all loads of a step issued together.
+// Algorithmic bytes: rows × E_pad / 8 read + the same written. Roofline: HBM.
+constexpr int K2A_UNROLL = 4;
 
-__device__ __forceinline__ word_result resolve_word(u64 word, u64 const e_base, u32 const * __restrict__ edge_src,
-	u32 const * __restrict__ edge_tgt, u32 cur)
-{
-	word_result r{0, 0, 0xffffffffu};
-	bool first(true);
-	while (word)
-	{
-		int const b(__ffsll((long long) word) - 1);
-		word &= word - 1;
-		u32 const s(edge_src[e_base + b]);
-		if (first) { r.s_first = s; first = false; }
-		if (s >= cur)
-		{
-			r.taken |= u64(1) << b;
-			cur = edge_tgt[e_base + b];
-		}
-	}
-	r.cur_out = cur;
-	return r;
-}
-
-// One warp per output row. lines = base of We-word lines; row i reads line line_idx[i] (PLOIDY_MAX → no ALT edges).
 __global__ void __launch_bounds__(256)
 resolve_rows_kernel(u64 const * __restrict__ lines, u32 const * __restrict__ line_idx, u32 const n_rows, u64 const We,
-	u32 const * __restrict__ edge_src, u32 const * __restrict__ edge_tgt, u64 * __restrict__ taken)
+	u64 const * __restrict__ edge_simple, u32 const * __restrict__ edge_src, u32 const * __restrict__ edge_tgt, u64 * __restrict__ taken)
 {
 	unsigned const lane(threadIdx.x & 31);
 	u32 const row((blockIdx.x * blockDim.x + threadIdx.x) >> 5);
@@ -160,46 +150,56 @@ resolve_rows_kernel(u64 const * __restrict__ lines, u32 const * __restrict__ lin
 		return;
 	}
 	u64 const *in(lines + u64(li) * We);
-	u32 carry(0);	// target node of the last taken edge so far
-	for (u64 wbase(0); wbase < We; wbase += 32)
+	int hist(-1);		// this lane's part of "index of the last taken edge so far" (the warp-wide maximum is the edge itself)
+	for (u64 wbase(0); wbase < We; wbase += 32 * K2A_UNROLL)
 	{
-		u64 const w(wbase + lane);
-		u64 const word(w < We ? in[w] : 0);
-		if (0 == __ballot_sync(0xffffffffu, 0 != word))
-		{
-			if (w < We) out[w] = 0;
-			continue;
-		}
-		// Optimistic pass: every lane resolves its word as if no earlier taken edge reached into it.
-		word_result res(resolve_word(word, 64 * w, edge_src, edge_tgt, 0));
-		u32 incl(word ? res.cur_out : 0);
+		u64 word[K2A_UNROLL], simple[K2A_UNROLL];
 #pragma unroll
-		for (int d = 1; d < 32; d <<= 1)
+		for (int k = 0; k < K2A_UNROLL; ++k)
 		{
-			u32 const o(__shfl_up_sync(0xffffffffu, incl, d));
-			if (lane >= unsigned(d)) incl = max(incl, o);
+			u64 const w(wbase + 32 * k + lane);
+			word[k] = w < We ? __ldcs(in + w) : 0;				// read once
+			simple[k] = w < We ? __ldg(edge_simple + w) : ~u64(0);	// shared by all rows
 		}
-		u32 excl(__shfl_up_sync(0xffffffffu, incl, 1));
-		if (0 == lane) excl = 0;
-		u32 const incoming(max(carry, excl));
-		bool const ok(0 == word || incoming <= res.s_first);
-		if (__all_sync(0xffffffffu, ok))
-			carry = max(carry, __shfl_sync(0xffffffffu, incl, 31));
-		else
+#pragma unroll
+		for (int k = 0; k < K2A_UNROLL; ++k)
 		{
-			// Some taken edge overlaps later set edges: replay the non-empty words in order with the true state.
-			unsigned m(__ballot_sync(0xffffffffu, 0 != word));
-			u32 c(carry);
+			u64 const w(wbase + 32 * k + lane);
+			u64 tk(word[k]);
+			int last(tk ? int(64 * u32(w)) + 63 - __clzll((long long) tk) : -1);	// last taken edge of this word if all its set edges are simple
+			unsigned m(__ballot_sync(0xffffffffu, 0 != (tk & ~simple[k])));
 			while (m)
 			{
+				// Lanes whose word has a set non-simple edge, in edge order: each needs the last taken edge before its word.
 				int const l(__ffs(m) - 1);
 				m &= m - 1;
-				if (int(lane) == l) res = resolve_word(word, 64 * w, edge_src, edge_tgt, c);
-				c = __shfl_sync(0xffffffffu, res.cur_out, l);
+				int const prev(__reduce_max_sync(0xffffffffu, max(hist, int(lane) < l ? last : -1)));
+				if (int(lane) == l)
+				{
+					int cur_e(prev);
+					bool known(false);
+					u32 cur_t(0);
+					u64 bits(tk), t(0);
+					last = -1;
+					while (bits)
+					{
+						int const b(__ffsll((long long) bits) - 1);
+						bits &= bits - 1;
+						u32 const e(64 * u32(w) + u32(b));
+						bool take(0 != (simple[k] >> b & 1));
+						if (!take)
+						{
+							if (!known) { cur_t = cur_e >= 0 ? edge_tgt[cur_e] : 0; known = true; }
+							take = edge_src[e] >= cur_t;
+						}
+						if (take) { t |= u64(1) << b; cur_e = int(e); known = false; last = int(e); }
+					}
+					tk = t;
+				}
 			}
-			carry = c;
+			hist = max(hist, last);
+			if (w < We) __stcs(out + w, tk);
 		}
-		if (w < We) out[w] = res.taken;
 	}
 }
 
@@ -573,7 +573,7 @@ int launch_resolve_rows(device_graph const &g, u64 const *d_lines, u32 const *d_
 	if (0 == n_rows || 0 == g.We) return 0;
 	unsigned const warps_per_cta(8);
 	resolve_rows_kernel<<<(n_rows + warps_per_cta - 1) / warps_per_cta, 32 * warps_per_cta, 0, stream>>>(
-		d_lines, d_line_idx, n_rows, g.We, g.edge_src, g.edge_tgt, d_taken);
+		d_lines, d_line_idx, n_rows, g.We, g.edge_simple, g.edge_src, g.edge_tgt, d_taken);
 	V2M_CHECK_LAUNCH("resolve_rows_kernel");
 	return 0;
 }

@@ -209,11 +209,147 @@ transpose_bits_tall_kernel(u64 const * __restrict__ src, u32 * __restrict__ dst,
 }
 
 
+// The streaming form of the same transpose, for long matrices (many source lines, few enough row bands to keep every band of a
+// stretch of lines resident at once). What bounds the two tile kernels above is not DRAM and not the bit work but the shape
+// of their stores (scripts/microbench/k1_patterns.cu, profiles/r02_k1_patterns.txt: the store pattern alone, with no loads
+// and no bit work, runs 1.55 ms on c5 — the whole kernel's time; reads alone 0.53 ms): 32-bit stores in 64-byte runs reach
+// 3.1 TB/s write-only when the runs start on sector boundaries and 2.0 – 2.4 TB/s when destination lines start mid-sector;
+// 64-bit stores in 128-byte runs that start on a sector boundary reach 5.4 – 5.6 TB/s on every shape.
+// Hence: (1) the transposed tile goes back to shared memory in destination order, so the stores need not follow the threads'
+// sub-tiles: a half warp writes one 128-byte run of one destination line with 64-bit stores; (2) run starts are moved back to
+// the 32-byte sector boundary below them (a destination line starts at row · C / 8, any multiple of 8), which takes the last
+// <= 24 bytes of the line's previous run: a CTA therefore walks consecutive line tiles of ONE row band and carries those
+// bytes from tile to tile in shared memory. Only the first run of a walk starts mid-sector and only its end flushes a partial
+// sector. (3) The source tile (1024 lines × 512 bits, the tall tile's swizzled layout) and the destination-order tile share
+// one 64 KiB buffer — the sub-tiles are in registers in between — so two CTAs fit an SM and one CTA's loads (issued for the
+// next tile before the stores of the current one) overlap the other's stores.
+// Grid: bands × walks, band fastest, at most two CTAs per SM so that all of it is resident; the bands of a walk then read
+// neighbouring 64-byte pieces of the same source lines at about the same time and share their boundary sectors in the L2.
+constexpr int K1S_LINES = 1024;								// source lines per tile
+constexpr int K1S_ROWS = 512;								// rows per band: 8 64-bit words of every source line
+constexpr int K1S_TILE_WORDS = K1S_LINES * 16 + 16;			// 32-bit words of the swizzled source tile (>= K1S_ROWS * 32)
+constexpr int K1S_SMEM = K1S_TILE_WORDS * 4 + K1S_ROWS * 32;	// + 32 carried bytes per row
+
+__device__ __forceinline__ void k1s_store(u8 *p, uint2 const v)
+{
+	asm volatile("st.global.v2.u32 [%0], {%1, %2};" :: "l"(p), "r"(v.x), "r"(v.y) : "memory");
+}
+
+__global__ void __launch_bounds__(K1_THREADS, 2)
+transpose_bits_stream_kernel(u64 const * __restrict__ src, u8 * __restrict__ dst, u64 const R64, u64 const C,
+	u32 const n_bands, u32 const walk_tiles, u32 const n_tiles)
+{
+	extern __shared__ __align__(16) u64 tile[];
+	u32 *tile32(reinterpret_cast<u32 *>(tile));
+	u8 *stage(reinterpret_cast<u8 *>(tile));					// [K1S_ROWS][128] once the sub-tiles are in registers
+	u8 *carry(stage + K1S_TILE_WORDS * 4);					// [K1S_ROWS][32]: the last 32 bytes of each row's previous run
+
+	unsigned const tid(threadIdx.x), lane(tid & 31), warp(tid >> 5);
+	u32 const band(blockIdx.x % n_bands), walk(blockIdx.x / n_bands);
+	u32 const x_begin(walk * walk_tiles), x_end(min(n_tiles, x_begin + walk_tiles));
+	u64 const LB(C / 8);										// bytes per destination line
+	u64 const R(64 * R64);
+	u64 const p0(u64(band) * (K1S_ROWS / 64));
+
+	unsigned const q(tid & 7), lp(tid >> 3);					// 64-bit word within the 64-byte piece of a line; 64 lines per pass
+	bool const pair_ok(p0 + q < R64);
+	u64 vals[K1S_LINES / 64];
+	auto const load_tile([&](u32 const x) {
+		u64 const c0(u64(x) * K1S_LINES);
+#pragma unroll
+		for (int p = 0; p < K1S_LINES / 64; ++p)
+		{
+			u64 const line(c0 + 64 * p + lp);
+			vals[p] = (pair_ok && line < C) ? __ldg(src + line * R64 + p0 + q) : 0;
+		}
+	});
+
+	unsigned const half(lane >> 4), l8(8 * (lane & 15));		// emission: a half warp per destination line, 8 bytes per lane
+	load_tile(x_begin);
+#pragma unroll 1
+	for (u32 x(x_begin); x < x_end; ++x)
+	{
+		// source tile → shared memory (transpose_bits_tall_kernel's layout)
+#pragma unroll
+		for (int p = 0; p < K1S_LINES / 64; ++p)
+		{
+			unsigned const l(64 * p + lp);
+			unsigned const sw((l >> 5) & 15);
+			u64 const v(vals[p]);
+			tile[l * 8 + 8 * (l >> 9) + (q ^ (sw >> 1))] = (sw & 1) ? (v >> 32 | v << 32) : v;
+		}
+		__syncthreads();
+		u32 a[32];
+		{
+			unsigned const base(32 * lane * 16 + 16 * (lane >> 4) + (warp ^ (lane & 15)));	// lane = line group, warp = word column
+#pragma unroll
+			for (int i = 0; i < 32; ++i)
+				a[i] = tile32[base + i * 16];
+		}
+		__syncthreads();											// every sub-tile is in registers: the buffer changes layout
+		transpose32(a);
+#pragma unroll
+		for (int j = 0; j < 32; ++j)
+			tile32[(32 * warp + j) * 32 + lane] = a[j];				// row 32 · warp + j of the band, word `lane` of its 128-byte run
+		__syncthreads();
+		if (x + 1 < x_end) load_tile(x + 1);						// in flight while this tile is stored
+
+		bool const first(x == x_begin), last(x + 1 == x_end);
+		u64 const X(u64(x) * (K1S_LINES / 8));						// byte offset of this tile's run in a destination line
+#pragma unroll 4
+		for (int it = 0; it < K1S_ROWS / 32; ++it)
+		{
+			unsigned const rl(32 * it + 2 * warp + half);
+			u64 const r(u64(band) * K1S_ROWS + rl);
+			u64 const line0(r * LB);
+			unsigned const s(unsigned(line0) & 31u);				// the line starts s bytes into a sector: its runs start s bytes early
+			bool const from_carry(l8 < s);
+			u8 const *from(from_carry ? carry + rl * 32 + (32 - s + l8) : stage + rl * 128 + (l8 - s));
+			uint2 const v(*reinterpret_cast<uint2 const *>(from));
+			u64 const o(X + l8 - s);								// wraps only where from_carry && first, which is not stored
+			if (r < R && !(from_carry && first) && o + 8 <= LB) k1s_store(dst + line0 + o, v);
+			if (last && from_carry)
+			{
+				// end of the walk: the bytes held back for the next run go out now
+				u64 const of(X + 128 - s + l8);
+				if (r < R && of + 8 <= LB) k1s_store(dst + line0 + of, *reinterpret_cast<uint2 const *>(stage + rl * 128 + (128 - s + l8)));
+			}
+			uint2 keep(v);
+			if (l8 >= 96) keep = *reinterpret_cast<uint2 const *>(stage + rl * 128 + l8);
+			__syncwarp();
+			if (l8 >= 96) *reinterpret_cast<uint2 *>(carry + rl * 32 + (l8 - 96)) = keep;
+		}
+		__syncthreads();											// the buffer is free for the next source tile
+	}
+}
+
+
 int launch_transpose_bits(void const *d_src, u64 rows, u64 cols, void *d_dst, cudaStream_t stream)
 {
 	if (0 == cols || 0 == rows) return 0;
 	u64 const R64(rows / 64);
-	static int const force([] { char const *env(std::getenv("V2M_K1_TALL")); return env ? std::atoi(env) : -1; }());	// experiments: 0 / 1
+	static int const force([] { char const *env(std::getenv("V2M_K1_TALL")); return env ? std::atoi(env) : -1; }());	// experiments: 0 / 1 / 2 (2: streaming kernel wherever its grid allows)
+	{
+		int dev(0), sms(0);
+		V2M_CUDA_TRY(cudaGetDevice(&dev));
+		V2M_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+		u64 const n_bands((rows + K1S_ROWS - 1) / K1S_ROWS), n_tiles((cols + K1S_LINES - 1) / K1S_LINES);
+		u64 const slots(2 * u64(sms));
+		// Long matrices with few row bands (the path matrix as build_variant_graph hands it over: rows = chromosome copies, one
+		// source line per edge): every band of a stretch of lines resident at once, >= 8 tiles per walk.
+		bool const streaming(force >= 0 ? 2 == force && n_bands <= slots : (n_bands <= slots && rows >= 1024 && n_tiles >= 8 * (slots / n_bands)));
+		if (streaming)
+		{
+			u64 const walks_wanted(std::max<u64>(1, slots / n_bands));
+			u32 const walk_tiles(u32((n_tiles + walks_wanted - 1) / walks_wanted));
+			u32 const n_walks(u32((n_tiles + walk_tiles - 1) / walk_tiles));
+			V2M_CUDA_TRY(cudaFuncSetAttribute(transpose_bits_stream_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, K1S_SMEM));
+			transpose_bits_stream_kernel<<<unsigned(n_bands * n_walks), K1_THREADS, K1S_SMEM, stream>>>(
+				static_cast<u64 const *>(d_src), static_cast<u8 *>(d_dst), R64, cols, u32(n_bands), walk_tiles, u32(n_tiles));
+			V2M_CHECK_LAUNCH("transpose_bits_stream_kernel");
+			return 0;
+		}
+	}
 	// Measured (scripts/bench_transpose.py, V2M_K1_TALL=0/1): the tall tiles win when the matrix has at most 512 rows (their
 	// 512-bit band wastes less of a short line: 64 × 4,096,000 runs 2.6 × faster) and when destination lines are an odd
 	// multiple of 8 bytes long (5056 × 3,000,000: 68 % against 61 % of the copy peak); they lose 6 points on sector-aligned

@@ -21,6 +21,31 @@ def row_range(n_rows: int, rank: int, world: int) -> tuple[int, int]:
     return begin, begin + base + (1 if rank < extra else 0)
 
 
+def shard_graph(graph, copy_begin: int, copy_end: int):
+    """The variant graph as one rank needs it: same nodes, edges and labels, the path matrices cut down to the 64-copy words
+    that cover chromosome copies [copy_begin, copy_end). Returns (sub_graph, copy_offset): chromosome copy c of the cohort is
+    copy c - copy_offset of sub_graph. A row of the output depends on its own line of paths_by_chrom_copy_and_edge only
+    (sequence_writer.cc:51-67 tests bit (edge, copy)), so the shard's rows are the cohort's rows — and a rank uploads
+    (copy_end - copy_begin) / H of the path bits instead of all of them."""
+    from .graph import VariantGraph
+    H = graph.total_chromosome_copies()
+    if not 0 <= copy_begin < copy_end <= H:
+        raise ValueError("chromosome copy range out of bounds")
+    w0, w1 = copy_begin // 64, (copy_end + 63) // 64
+    Wh, We = graph.h_pad // 64, graph.e_pad // 64
+    ec = ce = None
+    if graph.paths_by_edge_and_chrom_copy is not None:
+        ec = np.ascontiguousarray(graph.paths_by_edge_and_chrom_copy.reshape(graph.e_pad, Wh)[:, w0:w1]).reshape(-1)
+    if graph.paths_by_chrom_copy_and_edge is not None:
+        ce = np.ascontiguousarray(graph.paths_by_chrom_copy_and_edge[64 * w0 * We : 64 * w1 * We])
+    n_copies = min(H, 64 * w1) - 64 * w0
+    sub = VariantGraph(
+        graph.reference_positions, graph.aligned_positions, graph.alt_edge_targets, graph.alt_edge_count_csum, graph.label_offsets,
+        graph.label_chars, ec, ce, 64 * (w1 - w0), graph.e_pad, [f"copy{64 * w0 + i}" for i in range(n_copies)],
+        np.arange(n_copies + 1, dtype=np.uint32))
+    return sub, 64 * w0
+
+
 def row_offsets(ids, lengths) -> np.ndarray:
     """Byte offset of every row's '>' in the stream, plus the total size as the last entry."""
     sizes = np.array([1 + len(i.encode()) + 1 + int(n) + 1 for i, n in zip(ids, lengths)], np.int64)
