@@ -130,29 +130,59 @@ def model_row(a, taken, template=None):
     return bytes(row)
 
 
-def model_simple_edges(a):
-    """K2a's static property: edge e is simple iff no earlier edge's target node lies beyond src(e); a simple edge is taken
-    whenever its path bit is set."""
-    csum = a["alt_edge_count_csum"]
-    src = np.repeat(np.arange(len(csum) - 1), np.diff(csum).astype(np.int64))
+def model_edge_classes(a):
+    """K2a's static edge classes as graph_upload computes them: (simple, sibling) bit words (uint64 per 64 edges)."""
+    csum = np.asarray(a["alt_edge_count_csum"], np.int64)
     tgt = np.asarray(a["alt_edge_targets"], np.int64)
-    reach = np.concatenate([[0], np.maximum.accumulate(tgt)[:-1]]) if len(tgt) else np.zeros(0, np.int64)
-    return reach <= src
-
-
-def model_taken_edges_with_simple_mask(a, h, group=32 * 64):
-    """The walk as resolve_rows_kernel runs it: simple set edges are taken outright; a set non-simple edge is compared with the
-    target of the last taken edge (the taken edge with the largest index)."""
-    E = len(a["alt_edge_targets"])
     We = a["e_pad"] // 64
+    simple = [(1 << 64) - 1] * We
+    sibling = [0] * We
+    reach = 0
+    for n in range(len(csum) - 1):
+        lb, rb = int(csum[n]), int(csum[n + 1])
+        for e in range(lb, rb):
+            k = e - lb
+            if reach <= n and 1 <= k <= 3 and e % 64 >= k:
+                sibling[e // 64] |= 1 << (e % 64)
+            elif reach > n or k >= 1:
+                simple[e // 64] &= ~(1 << (e % 64))
+        for e in range(lb, rb):
+            reach = max(reach, int(tgt[e]))
+    return simple, sibling
+
+
+def model_taken_edges_by_classes(a, h):
+    """The walk as resolve_rows_kernel runs it, word by word: simple and sibling edges by bit arithmetic, complex edges by the
+    walk's rule against the target of the last taken edge (the taken edge with the largest index)."""
+    We = a["e_pad"] // 64
+    M = (1 << 64) - 1
     csum = a["alt_edge_count_csum"]
     src = np.repeat(np.arange(len(csum) - 1), np.diff(csum).astype(np.int64))
-    simple = model_simple_edges(a)
+    tgt = a["alt_edge_targets"]
+    simple, sibling = model_edge_classes(a)
     taken, last = [], -1
-    for e in range(E):
-        if not bit(a["paths_ce"], We, h, e):
-            continue
-        if simple[e] or src[e] >= (int(a["alt_edge_targets"][last]) if last >= 0 else 0):
-            taken.append(e)
-            last = e
+    for w in range(We):
+        S = int(a["paths_ce"][h * We + w])
+        m1 = sibling[w]
+        m2 = m1 & (m1 << 1) & M
+        m3 = m2 & (m1 << 2) & M
+        fast = S & ~((((S << 1) & m1) | ((S << 2) & m2) | ((S << 3) & m3)) & M)
+        tk = fast
+        if S & ~simple[w] & M:
+            tk, cur = 0, last
+            for b in range(64):
+                if not (S >> b) & 1:
+                    continue
+                e = 64 * w + b
+                if (simple[w] >> b) & 1:
+                    take = bool((fast >> b) & 1)
+                else:
+                    take = int(src[e]) >= (int(tgt[cur]) if cur >= 0 else 0)
+                if take:
+                    tk |= 1 << b
+                    cur = e
+        for b in range(64):
+            if (tk >> b) & 1:
+                taken.append(64 * w + b)
+                last = 64 * w + b
     return taken

@@ -28,13 +28,16 @@ def test_overlaps_are_exercised(tmp_path):
     assert n > 20
 
 
-@pytest.mark.parametrize("seed", range(30))
-def test_simple_edges_need_no_walk_state(tmp_path, seed):
-    """K2a (resolve_rows_kernel) decides set bits of 'simple' edges without loading anything: check the rule against the walk."""
-    g = rg.random_oracle_graph(str(tmp_path), 100 + seed, ref_len=200 + 9 * seed, n_records=20 + 2 * seed, n_samples=5,
-                               ploidy=1 + seed % 2, long_del_prob=0.08 if seed % 2 else 0.0, many_alts_prob=0.2 if seed % 3 == 0 else 0.0)
+@pytest.mark.parametrize("seed", range(36))
+def test_edge_classes_need_no_walk_state(tmp_path, seed):
+    """K2a (resolve_rows_kernel) decides set bits of simple and sibling edges without loading anything: check its word
+    arithmetic and the complex-edge fallback against the walk, on graphs with many multi-allelic sites and overlaps."""
+    g = rg.random_oracle_graph(str(tmp_path), 100 + seed, ref_len=200 + 9 * seed, n_records=20 + 3 * seed, n_samples=5,
+                               ploidy=1 + seed % 2, long_del_prob=0.08 if seed % 2 else 0.0, many_alts_prob=0.3 if seed % 3 == 0 else 0.0,
+                               alt_freq=0.5 if seed % 4 == 0 else 0.3)
     a = g.arrays()
-    simple = rg.model_simple_edges(a)
-    assert simple.any() and (not simple.all() or seed % 2 == 0)
+    simple, sibling = rg.model_edge_classes(a)
+    E = len(a["alt_edge_targets"])
+    assert any(simple) and (seed % 3 != 0 or any(sibling))
     for h in range(a["total_copies"]):
-        assert rg.model_taken_edges_with_simple_mask(a, h) == rg.model_taken_edges(a, h), (seed, h)
+        assert rg.model_taken_edges_by_classes(a, h) == rg.model_taken_edges(a, h), (seed, h)

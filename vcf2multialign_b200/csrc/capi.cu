@@ -206,8 +206,9 @@ int v2m_cuda_graph_upload(const v2m_graph_view *view, v2m_graph_t *out)
 	}
 	std::vector<edge_rec> edges(g.e_pad, edge_rec{0, 0, 0, 0});
 	std::vector<uint2> edge_ref(g.e_pad, make_uint2(0, 0));
-	std::vector<u64> edge_simple(g.We, ~u64(0));	// K2a: bit e clear iff some earlier edge's target lies beyond src(e)
-	u64 reach(0);									// max target node over the edges seen so far
+	// K2a's edge classes (emit_rows.cu): simple / sibling / complex
+	std::vector<u64> edge_simple(g.We, ~u64(0)), edge_sibling(g.We, 0);
+	u64 reach(0);									// max target node over the edges of earlier nodes
 	for (u64 n(0); n < N; ++n)
 	{
 		u64 const lb(holder->csum[n]), rb(holder->csum[n + 1]);
@@ -221,11 +222,13 @@ int v2m_cuda_graph_upload(const v2m_graph_view *view, v2m_graph_t *out)
 				return fail(V2M_ERR_ARGUMENT, "graph_upload: ALT label longer than its aligned span (sequence_writer.cc:61)");
 			if (hi >= (u64(1) << 32)) return fail(V2M_ERR_ARGUMENT, "graph_upload: label store too large");
 			edge_src[e] = u32(n); edge_tgt[e] = u32(t);
-			if (reach > n) edge_simple[e / 64] &= ~(u64(1) << (e % 64));
-			reach = std::max(reach, t);
+			u64 const k(e - lb);					// 0: the node's first ALT edge
+			if (reach <= n && k >= 1 && k <= 3 && e % 64 >= k) edge_sibling[e / 64] |= u64(1) << (e % 64);
+			else if (reach > n || k >= 1) edge_simple[e / 64] &= ~(u64(1) << (e % 64));
 			edges[e] = edge_rec{alnpos[n], alnpos[t], u32(lo), u32(hi - lo)};
 			edge_ref[e] = make_uint2(refpos[n], refpos[t]);
 		}
+		for (u64 e(lb); e < rb; ++e) reach = std::max<u64>(reach, view->alt_edge_targets[e]);
 	}
 	g.label_bytes = E ? view->label_offsets[E] : 0;
 
@@ -265,6 +268,7 @@ int v2m_cuda_graph_upload(const v2m_graph_view *view, v2m_graph_t *out)
 	if (int const st = dev_upload(g.edge_src, edge_src.data(), g.e_pad)) return st;
 	if (int const st = dev_upload(g.edge_tgt, edge_tgt.data(), g.e_pad)) return st;
 	if (int const st = dev_upload(g.edge_simple, edge_simple.data(), g.We)) return st;
+	if (int const st = dev_upload(g.edge_sibling, edge_sibling.data(), g.We)) return st;
 	if (int const st = dev_upload(g.edges, edges.data(), g.e_pad)) return st;
 	if (int const st = dev_upload(g.label_chars, reinterpret_cast<u8 const *>(view->label_chars), g.label_bytes, g.label_bytes + 32)) return st;
 	if (int const st = dev_upload(g.tile_edges, tile_edges.data(), tile_edges.size())) return st;

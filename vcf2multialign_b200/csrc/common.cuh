@@ -7,6 +7,10 @@
 
 #include <cuda_runtime.h>
 
+#ifndef V2M_T32_MULHI
+#define V2M_T32_MULHI 0
+#endif
+
 namespace v2m {
 
 using u8 = std::uint8_t;
@@ -150,9 +154,20 @@ __host__ __device__ __forceinline__ void transpose32(u32 (&a)[32])
 #pragma unroll
 		for (int k = 0; k < 32; k = (k + j + 1) & ~j)
 		{
+#ifdef __CUDA_ARCH__
+			// two shifts + two bit selects (LOP3) per pair; m << j == ~m for these masks
+			u32 const x(a[k]), y(a[k + j]);
+			a[k] = (x & m) | ((y << j) & ~m);
+#if V2M_T32_MULHI
+			a[k + j] = (__umulhi(x, 1u << (32 - j)) & m) | (y & ~m);	// x >> j on the FMA pipe (IMAD.HI): the ALU pipe is the busy one in K1
+#else
+			a[k + j] = ((x >> j) & m) | (y & ~m);
+#endif
+#else
 			u32 const t(((a[k] >> j) ^ a[k + j]) & m);
 			a[k + j] ^= t;
 			a[k] ^= (t << j);
+#endif
 		}
 	}
 }

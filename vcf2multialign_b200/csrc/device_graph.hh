@@ -5,8 +5,10 @@
 //   alnpos       N × u32                               aligned_positions (A = alnpos[N-1] < 2^32)
 //   edge_src     E_pad × u32                           source node of each ALT edge (from alt_edge_count_csum)
 //   edge_tgt     E_pad × u32                           alt_edge_targets
-//   edge_simple  E_pad bits                            1 = no earlier edge's target lies beyond this edge's source node: the walk
-//                                                      takes it whenever its path bit is set (K2a)
+//   edge_simple  E_pad bits                            1 = K2a decides the edge without the walk's state: first ALT edge of a node no
+//                                                      earlier node's edge reaches beyond (taken whenever set), or a sibling:
+//   edge_sibling E_pad bits                            1 = 2nd … 4th ALT edge of such a node, same 64-edge word as the first (taken
+//                                                      iff set and no earlier edge of the node is set)
 //   edges        E_pad × 16 B  (edge_rec)              aligned span [aln[src], aln[tgt]) + label offset/length
 //   label_chars  Σ|label| bytes                        alt_edge_labels, flattened
 //   paths_eh     E_pad × (H_pad/64) × u64              paths_by_edge_and_chrom_copy.values(): one line per edge
@@ -47,7 +49,8 @@ struct device_graph
 	u8			*ref{};
 	u32			*refpos{}, *alnpos{};
 	u32			*edge_src{}, *edge_tgt{};
-	u64			*edge_simple{};				// E_pad bits: no earlier edge reaches beyond this edge's source node (K2a)
+	u64			*edge_simple{};				// E_pad bits: decided without the walk's state (first ALT of a clean node, or a sibling below) (K2a)
+	u64			*edge_sibling{};			// E_pad bits: 2nd … 4th ALT of a clean node whose earlier ALTs lie in the same 64-edge word (K2a)
 	edge_rec	*edges{};
 	u8			*label_chars{};
 	u64			*paths_eh{}, *paths_he{};
@@ -96,7 +99,7 @@ struct graph_holder
 
 	~graph_holder()
 	{
-		cudaFree(g.edge_simple); cudaFree(g.ref); cudaFree(g.refpos); cudaFree(g.alnpos); cudaFree(g.edge_src); cudaFree(g.edge_tgt);
+		cudaFree(g.edge_simple); cudaFree(g.edge_sibling); cudaFree(g.ref); cudaFree(g.refpos); cudaFree(g.alnpos); cudaFree(g.edge_src); cudaFree(g.edge_tgt);
 		cudaFree(g.edges); cudaFree(g.label_chars); cudaFree(g.paths_eh); cudaFree(g.paths_he);
 		cudaFree(g.tmpl); cudaFree(g.tile_edges); cudaFree(g.tile_labels); cudaFree(g.edge_ref); cudaFree(g.ref_tile_edges);
 	}

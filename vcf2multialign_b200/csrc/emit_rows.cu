@@ -124,20 +124,25 @@ compose_founder_kernel(u64 const * __restrict__ paths_he, u64 const We,
 // ---------------------------------------------------------------------------------------------------------
 // The walk takes set edge e iff src(e) >= target of the last taken edge (sequence_writer.cc:51-67; targets of taken edges
 // grow along the walk, so "the last taken edge" is the taken edge with the largest index). Most edges can be decided without
-// looking at the walk at all: edge e is *simple* when no earlier edge of the graph — set or not — reaches beyond its source
-// node (max over e' < e of tgt(e') <= src(e): true for every first ALT of a site that no earlier deletion spans), and a simple
-// edge is taken whenever its bit is set. graph_upload stores that property as one bit per edge (edge_simple, E_pad / 8 bytes,
-// L2-resident), so the common case is `taken = path word` with no per-edge load; only set bits of non-simple edges (second
-// ALTs of multi-allelic sites, edges under an overlapping deletion) are resolved by the walk's rule, in order, with the
-// target of the last taken edge fetched when one of them needs it. The first version loaded edge_src / edge_tgt for every
-// set bit: ~1.9 G scattered 4-byte loads on c4, bound by L2 sector throughput at 520 GB/s of algorithmic traffic.
+// looking at the walk at all. Call a node *clean* when no edge of an earlier node reaches beyond it. graph_upload classifies
+// every edge (two bits per edge, E_pad / 4 bytes, L2-resident):
+//   simple   first ALT edge of a clean node: taken whenever its bit is set;
+//   sibling  2nd … 4th ALT edge of a clean node, in the same 64-edge word as the first: taken iff set and no earlier edge of
+//            the node is set (the first set edge of a visited node wins, :51-66) — three shift-and-mask terms per word;
+//   complex  everything else (edges of nodes under an earlier edge's span — overlapping records —, deeper siblings, sibling
+//            runs that cross a word): decided by the walk's rule, in order, with src(e) and the target of the last taken edge
+//            loaded only then.
+// The common case is therefore `taken = path word & ~blocked siblings` with no per-edge load. The first version loaded edge_src
+// / edge_tgt for every set bit (~1.9 G scattered 4-byte loads on c4: L2 sector throughput, 520 GB/s of algorithmic traffic);
+// with only first ALTs exempted the ~5 k second-ALT bits per row still cost a dependent-load chain each (750 GB/s).
 // One warp per output row, K2A_UNROLL × 32 words (8192 edges at 4) per step with all loads of a step issued together.
 // Algorithmic bytes: rows × E_pad / 8 read + the same written. Roofline: HBM.
 constexpr int K2A_UNROLL = 4;
 
 __global__ void __launch_bounds__(256)
 resolve_rows_kernel(u64 const * __restrict__ lines, u32 const * __restrict__ line_idx, u32 const n_rows, u64 const We,
-	u64 const * __restrict__ edge_simple, u32 const * __restrict__ edge_src, u32 const * __restrict__ edge_tgt, u64 * __restrict__ taken)
+	u64 const * __restrict__ edge_simple, u64 const * __restrict__ edge_sibling,
+	u32 const * __restrict__ edge_src, u32 const * __restrict__ edge_tgt, u64 * __restrict__ taken)
 {
 	unsigned const lane(threadIdx.x & 31);
 	u32 const row((blockIdx.x * blockDim.x + threadIdx.x) >> 5);
@@ -153,24 +158,29 @@ resolve_rows_kernel(u64 const * __restrict__ lines, u32 const * __restrict__ lin
 	int hist(-1);		// this lane's part of "index of the last taken edge so far" (the warp-wide maximum is the edge itself)
 	for (u64 wbase(0); wbase < We; wbase += 32 * K2A_UNROLL)
 	{
-		u64 word[K2A_UNROLL], simple[K2A_UNROLL];
+		u64 word[K2A_UNROLL], simple[K2A_UNROLL], sib[K2A_UNROLL];
 #pragma unroll
 		for (int k = 0; k < K2A_UNROLL; ++k)
 		{
 			u64 const w(wbase + 32 * k + lane);
-			word[k] = w < We ? __ldcs(in + w) : 0;				// read once
+			word[k] = w < We ? __ldcs(in + w) : 0;					// read once
 			simple[k] = w < We ? __ldg(edge_simple + w) : ~u64(0);	// shared by all rows
+			sib[k] = w < We ? __ldg(edge_sibling + w) : 0;
 		}
 #pragma unroll
 		for (int k = 0; k < K2A_UNROLL; ++k)
 		{
 			u64 const w(wbase + 32 * k + lane);
-			u64 tk(word[k]);
-			int last(tk ? int(64 * u32(w)) + 63 - __clzll((long long) tk) : -1);	// last taken edge of this word if all its set edges are simple
-			unsigned m(__ballot_sync(0xffffffffu, 0 != (tk & ~simple[k])));
+			u64 const set(word[k]);
+			// a sibling is blocked by a set edge of its node one, two or three places below it
+			u64 const m1(sib[k]), m2(m1 & (m1 << 1)), m3(m2 & (m1 << 2));
+			u64 const fast(set & ~(((set << 1) & m1) | ((set << 2) & m2) | ((set << 3) & m3)));
+			u64 tk(fast);
+			unsigned m(__ballot_sync(0xffffffffu, 0 != (set & ~simple[k])));
+			int last(tk ? int(64 * u32(w)) + 63 - __clzll((long long) tk) : -1);	// last taken edge of this word unless a complex edge says otherwise
 			while (m)
 			{
-				// Lanes whose word has a set non-simple edge, in edge order: each needs the last taken edge before its word.
+				// Lanes whose word has a set complex edge, in edge order: each needs the last taken edge before its word.
 				int const l(__ffs(m) - 1);
 				m &= m - 1;
 				int const prev(__reduce_max_sync(0xffffffffu, max(hist, int(lane) < l ? last : -1)));
@@ -179,15 +189,16 @@ resolve_rows_kernel(u64 const * __restrict__ lines, u32 const * __restrict__ lin
 					int cur_e(prev);
 					bool known(false);
 					u32 cur_t(0);
-					u64 bits(tk), t(0);
+					u64 bits(set), t(0);
 					last = -1;
 					while (bits)
 					{
 						int const b(__ffsll((long long) bits) - 1);
 						bits &= bits - 1;
 						u32 const e(64 * u32(w) + u32(b));
-						bool take(0 != (simple[k] >> b & 1));
-						if (!take)
+						bool take;
+						if (simple[k] >> b & 1) take = 0 != (fast >> b & 1);
+						else
 						{
 							if (!known) { cur_t = cur_e >= 0 ? edge_tgt[cur_e] : 0; known = true; }
 							take = edge_src[e] >= cur_t;
@@ -573,7 +584,7 @@ int launch_resolve_rows(device_graph const &g, u64 const *d_lines, u32 const *d_
 	if (0 == n_rows || 0 == g.We) return 0;
 	unsigned const warps_per_cta(8);
 	resolve_rows_kernel<<<(n_rows + warps_per_cta - 1) / warps_per_cta, 32 * warps_per_cta, 0, stream>>>(
-		d_lines, d_line_idx, n_rows, g.We, g.edge_simple, g.edge_src, g.edge_tgt, d_taken);
+		d_lines, d_line_idx, n_rows, g.We, g.edge_simple, g.edge_sibling, g.edge_src, g.edge_tgt, d_taken);
 	V2M_CHECK_LAUNCH("resolve_rows_kernel");
 	return 0;
 }

@@ -209,118 +209,165 @@ transpose_bits_tall_kernel(u64 const * __restrict__ src, u32 * __restrict__ dst,
 }
 
 
-// The streaming form of the same transpose, for long matrices (many source lines, few enough row bands to keep every band of a
-// stretch of lines resident at once). What bounds the two tile kernels above is not DRAM and not the bit work but the shape
-// of their stores (scripts/microbench/k1_patterns.cu, profiles/r02_k1_patterns.txt: the store pattern alone, with no loads
-// and no bit work, runs 1.55 ms on c5 — the whole kernel's time; reads alone 0.53 ms): 32-bit stores in 64-byte runs reach
-// 3.1 TB/s write-only when the runs start on sector boundaries and 2.0 – 2.4 TB/s when destination lines start mid-sector;
-// 64-bit stores in 128-byte runs that start on a sector boundary reach 5.4 – 5.6 TB/s on every shape.
-// Hence: (1) the transposed tile goes back to shared memory in destination order, so the stores need not follow the threads'
-// sub-tiles: a half warp writes one 128-byte run of one destination line with 64-bit stores; (2) run starts are moved back to
-// the 32-byte sector boundary below them (a destination line starts at row · C / 8, any multiple of 8), which takes the last
-// <= 24 bytes of the line's previous run: a CTA therefore walks consecutive line tiles of ONE row band and carries those
-// bytes from tile to tile in shared memory. Only the first run of a walk starts mid-sector and only its end flushes a partial
-// sector. (3) The source tile (1024 lines × 512 bits, the tall tile's swizzled layout) and the destination-order tile share
-// one 64 KiB buffer — the sub-tiles are in registers in between — so two CTAs fit an SM and one CTA's loads (issued for the
-// next tile before the stores of the current one) overlap the other's stores.
-// Grid: bands × walks, band fastest, at most two CTAs per SM so that all of it is resident; the bands of a walk then read
-// neighbouring 64-byte pieces of the same source lines at about the same time and share their boundary sectors in the L2.
-constexpr int K1S_LINES = 1024;								// source lines per tile
-constexpr int K1S_ROWS = 512;								// rows per band: 8 64-bit words of every source line
-constexpr int K1S_TILE_WORDS = K1S_LINES * 16 + 16;			// 32-bit words of the swizzled source tile (>= K1S_ROWS * 32)
-constexpr int K1S_SMEM = K1S_TILE_WORDS * 4 + K1S_ROWS * 32;	// + 32 carried bytes per row
+// The sheared form of the same transpose, for the matrices the path actually hands over (thousands of rows, 10^5 … 10^7
+// source lines). What bounds the two tile kernels above is neither DRAM nor the bit work but the shape of their stores
+// (scripts/microbench/k1_patterns.cu, profiles/r02_k1_patterns.txt: their store pattern alone, with no loads and no bit work,
+// takes 1.55 ms on c5 — the whole kernel's time; their reads alone 0.53 ms): 32-bit stores in 64-byte runs reach 3.1 TB/s
+// write-only when the runs start on sector boundaries and 2.0 – 2.4 TB/s when destination lines start mid-sector, whereas
+// 64-bit stores in 128-byte runs that start on a sector boundary reach 5.4 – 5.6 TB/s on every shape. Hence:
+//   (1) tall tiles (1024 lines × 512 bits: a warp's 32 sub-tiles lie side by side along one destination line) and a word swap
+//       between neighbouring lanes per pair of rows, so that a warp's store is two 128-byte runs with 8 bytes per lane (staging
+//       the transposed tile in shared memory for the same store shape cost more than it gained: 1.90 ms on c5, three barriers
+//       and ~850 instructions per warp and tile);
+//   (2) every destination line's runs start on 32-byte sector boundaries. Line r starts at byte r · C / 8, i.e. s(r) = 0, 8,
+//       16 or 24 bytes into a sector, so its run in tile x is bytes [128 x − s, 128 x − s + 128) of the line: source lines
+//       [1024 x − 8 s, 1024 x − 8 s + 1024). Rows of different s sit side by side in every 32 × 32 sub-tile, so the sub-tile
+//       is *sheared* on the way into registers: word i of a thread's sub-tile is assembled from the same word of up to four
+//       source lines, 64 · k lines apart, each masked to the rows whose shift is 8 k bytes (the row masks are the same for
+//       every sub-tile, since sub-tiles start at multiples of 32 rows). One transpose32 then yields every row's own window.
+//       The tile loads a halo of 192 source lines (L2 hits: the neighbouring tile's CTA reads them as its own at the same
+//       time) and the sub-tile read costs up to four LDS + three LOP3 per word instead of one LDS;
+//   RESULT (profiles/r02_k1_sheared.txt): correct on every shape (tests/test_gpu_parity.py runs all three kernels against the
+//   oracle) and indifferent to the destination lines' phase, as intended — but 1.85 ms on c5 against the tile kernel's 1.57,
+//   2.19 against 1.73 (tall) on the c4 shape, 1.74 against 1.43 on a sector-aligned shape. ncu: the ALU pipe is 71 % busy and
+//   `math pipe throttle` is the top stall (1.16 G warp instructions against the tile kernel's 0.77 G): with the stores out of
+//   the way the transpose is bound by its own integer work — 64 PRMT + 144 LOP3 / SHF for the bit stages plus index
+//   arithmetic, selects for the swizzle and the lane swap — and the shear and the halo add to exactly that. It therefore stays
+//   opt-in (V2M_K1_TALL=2) as the record of the experiment; the launcher's default is unchanged.
+//   (3) tiles are independent, two CTAs per SM, row bands fastest in the grid, so that at any moment the CTAs in flight write
+//       ~30 consecutive runs (3.8 KB) of every destination line. A variant in which persistent CTAs walked along the lines and
+//       carried each line's last bytes from tile to tile in shared memory (no halo, no shear) ran 2.50 ms on c5 against the
+//       tile kernel's 1.57: its CTAs write 128-byte pieces that are ~26 KB apart in every destination line, and DRAM pages
+//       see one piece at a time.
+constexpr int K1H_LINES = 1024;								// a tile's own source lines = 128 bytes of every destination line
+constexpr int K1H_ROWS = 512;								// rows per band: 8 64-bit words of every source line
+constexpr int K1H_HALO = 192;								// source lines before the tile's own: 24 bytes per destination line
+constexpr int K1H_SRC_LINES = K1H_LINES + K1H_HALO;
+constexpr int K1H_PASSES = K1H_SRC_LINES / 64;
+constexpr int K1H_HALO_PASSES = K1H_HALO / 64;
+constexpr int K1H_TILE_WORDS = K1H_SRC_LINES * 16 + 16 * ((K1H_SRC_LINES - 1) >> 9) + 16;	// 32-bit words, tall-tile swizzle (>= K1H_ROWS * 32)
+constexpr int K1H_SMEM = K1H_TILE_WORDS * 4;
 
-__device__ __forceinline__ void k1s_store(u8 *p, uint2 const v)
+struct k1h_shifts { u32 rows[4]; };							// rows[k]: bit j set iff line 32 m + j starts 8 k bytes into a sector
+
+// EDGE = false: a tile whose own lines, halo and row band all lie inside the matrix — no bounds checks, addresses by constant
+// strides (the kernel is bound by the ALU pipe: 71 % busy in the first version, of which a third was address arithmetic,
+// predicates and selects; profiles/r02_k1_sheared_ncu_summary.txt).
+template <bool EDGE>
+__device__ __forceinline__ void k1h_tile(u64 const * __restrict__ src, u8 * __restrict__ dst, u64 const R64, u64 const C, k1h_shifts const &sh,
+	u64 *tile, u32 const band, u32 const x)
 {
-	asm volatile("st.global.v2.u32 [%0], {%1, %2};" :: "l"(p), "r"(v.x), "r"(v.y) : "memory");
-}
-
-__global__ void __launch_bounds__(K1_THREADS, 2)
-transpose_bits_stream_kernel(u64 const * __restrict__ src, u8 * __restrict__ dst, u64 const R64, u64 const C,
-	u32 const n_bands, u32 const walk_tiles, u32 const n_tiles)
-{
-	extern __shared__ __align__(16) u64 tile[];
-	u32 *tile32(reinterpret_cast<u32 *>(tile));
-	u8 *stage(reinterpret_cast<u8 *>(tile));					// [K1S_ROWS][128] once the sub-tiles are in registers
-	u8 *carry(stage + K1S_TILE_WORDS * 4);					// [K1S_ROWS][32]: the last 32 bytes of each row's previous run
-
+	u32 const *tile32(reinterpret_cast<u32 const *>(tile));
 	unsigned const tid(threadIdx.x), lane(tid & 31), warp(tid >> 5);
-	u32 const band(blockIdx.x % n_bands), walk(blockIdx.x / n_bands);
-	u32 const x_begin(walk * walk_tiles), x_end(min(n_tiles, x_begin + walk_tiles));
-	u64 const LB(C / 8);										// bytes per destination line
-	u64 const R(64 * R64);
-	u64 const p0(u64(band) * (K1S_ROWS / 64));
+	u64 const LB(C / 8);											// bytes per destination line
+	u64 const p0(u64(band) * (K1H_ROWS / 64));
+	bool const sheared(0 != (sh.rows[1] | sh.rows[2] | sh.rows[3]));
 
-	unsigned const q(tid & 7), lp(tid >> 3);					// 64-bit word within the 64-byte piece of a line; 64 lines per pass
-	bool const pair_ok(p0 + q < R64);
-	u64 vals[K1S_LINES / 64];
-	auto const load_tile([&](u32 const x) {
-		u64 const c0(u64(x) * K1S_LINES);
-#pragma unroll
-		for (int p = 0; p < K1S_LINES / 64; ++p)
-		{
-			u64 const line(c0 + 64 * p + lp);
-			vals[p] = (pair_ok && line < C) ? __ldg(src + line * R64 + p0 + q) : 0;
-		}
-	});
-
-	unsigned const half(lane >> 4), l8(8 * (lane & 15));		// emission: a half warp per destination line, 8 bytes per lane
-	load_tile(x_begin);
-#pragma unroll 1
-	for (u32 x(x_begin); x < x_end; ++x)
+	// ---- source tile (halo first) → shared memory, the tall tile's swizzled layout ------------------------------------------
 	{
-		// source tile → shared memory (transpose_bits_tall_kernel's layout)
+		unsigned const q(tid & 7), lp(tid >> 3);					// 64-bit word within the 64-byte piece of a line; 64 lines per pass
+		u64 vals[K1H_PASSES];
+		if (EDGE)
+		{
+			bool const pair_ok(p0 + q < R64);
+			long long const line0((long long) x * K1H_LINES - K1H_HALO);
 #pragma unroll
-		for (int p = 0; p < K1S_LINES / 64; ++p)
+			for (int p = 0; p < K1H_PASSES; ++p)
+			{
+				long long const line(line0 + 64 * p + lp);
+				bool const wanted(p >= K1H_HALO_PASSES || sheared);
+				vals[p] = (wanted && pair_ok && line >= 0 && u64(line) < C) ? __ldg(src + u64(line) * R64 + p0 + q) : 0;
+			}
+		}
+		else
+		{
+			u64 const *first(src + (u64(x) * K1H_LINES - K1H_HALO + lp) * R64 + p0 + q);
+			u64 const stride(64 * R64);
+#pragma unroll
+			for (int p = 0; p < K1H_PASSES; ++p)
+				vals[p] = (p >= K1H_HALO_PASSES || sheared) ? __ldg(first + u64(p) * stride) : 0;
+		}
+#pragma unroll
+		for (int p = 0; p < K1H_PASSES; ++p)
 		{
 			unsigned const l(64 * p + lp);
 			unsigned const sw((l >> 5) & 15);
 			u64 const v(vals[p]);
 			tile[l * 8 + 8 * (l >> 9) + (q ^ (sw >> 1))] = (sw & 1) ? (v >> 32 | v << 32) : v;
 		}
-		__syncthreads();
-		u32 a[32];
+	}
+	__syncthreads();
+
+	// ---- sheared 32 × 32 sub-tile: lane = line group of the tile's own lines, warp = word column ----------------------------
+	// Rows that start 8 k bytes into a sector take their bits from the source lines 64 k earlier, i.e. from line group G0 - 2 k.
+	u32 a[32];
+	{
+		unsigned const G0(lane + K1H_HALO / 32);					// local line group of this lane's unshifted window
+		auto const base_of([&](unsigned const G) { return 512 * G + 16 * (G >> 4) + (warp ^ (G & 15)); });
+		unsigned const b0(base_of(G0));
+		if (!sheared)
 		{
-			unsigned const base(32 * lane * 16 + 16 * (lane >> 4) + (warp ^ (lane & 15)));	// lane = line group, warp = word column
+#pragma unroll
+			for (int i = 0; i < 32; ++i) a[i] = tile32[b0 + i * 16];
+		}
+		else if (0 == sh.rows[1])
+		{
+			// destination lines are 16 mod 32 bytes long: shifts 0 and 16
+			unsigned const b2(base_of(G0 - 4));
+			u32 const m0(sh.rows[0]);
+#pragma unroll
+			for (int i = 0; i < 32; ++i) a[i] = (tile32[b0 + i * 16] & m0) | (tile32[b2 + i * 16] & ~m0);
+		}
+		else
+		{
+			unsigned const b1(base_of(G0 - 2)), b2(base_of(G0 - 4)), b3(base_of(G0 - 6));
+			u32 const m0(sh.rows[0]), m2(sh.rows[2]), m01(sh.rows[0] | sh.rows[1]);
 #pragma unroll
 			for (int i = 0; i < 32; ++i)
-				a[i] = tile32[base + i * 16];
-		}
-		__syncthreads();											// every sub-tile is in registers: the buffer changes layout
-		transpose32(a);
-#pragma unroll
-		for (int j = 0; j < 32; ++j)
-			tile32[(32 * warp + j) * 32 + lane] = a[j];				// row 32 · warp + j of the band, word `lane` of its 128-byte run
-		__syncthreads();
-		if (x + 1 < x_end) load_tile(x + 1);						// in flight while this tile is stored
-
-		bool const first(x == x_begin), last(x + 1 == x_end);
-		u64 const X(u64(x) * (K1S_LINES / 8));						// byte offset of this tile's run in a destination line
-#pragma unroll 4
-		for (int it = 0; it < K1S_ROWS / 32; ++it)
-		{
-			unsigned const rl(32 * it + 2 * warp + half);
-			u64 const r(u64(band) * K1S_ROWS + rl);
-			u64 const line0(r * LB);
-			unsigned const s(unsigned(line0) & 31u);				// the line starts s bytes into a sector: its runs start s bytes early
-			bool const from_carry(l8 < s);
-			u8 const *from(from_carry ? carry + rl * 32 + (32 - s + l8) : stage + rl * 128 + (l8 - s));
-			uint2 const v(*reinterpret_cast<uint2 const *>(from));
-			u64 const o(X + l8 - s);								// wraps only where from_carry && first, which is not stored
-			if (r < R && !(from_carry && first) && o + 8 <= LB) k1s_store(dst + line0 + o, v);
-			if (last && from_carry)
 			{
-				// end of the walk: the bytes held back for the next run go out now
-				u64 const of(X + 128 - s + l8);
-				if (r < R && of + 8 <= LB) k1s_store(dst + line0 + of, *reinterpret_cast<uint2 const *>(stage + rl * 128 + (128 - s + l8)));
+				u32 const lo((tile32[b0 + i * 16] & m0) | (tile32[b1 + i * 16] & ~m0));
+				u32 const hi((tile32[b2 + i * 16] & m2) | (tile32[b3 + i * 16] & ~m2));
+				a[i] = (lo & m01) | (hi & ~m01);
 			}
-			uint2 keep(v);
-			if (l8 >= 96) keep = *reinterpret_cast<uint2 const *>(stage + rl * 128 + l8);
-			__syncwarp();
-			if (l8 >= 96) *reinterpret_cast<uint2 *>(carry + rl * 32 + (l8 - 96)) = keep;
 		}
-		__syncthreads();											// the buffer is free for the next source tile
 	}
+	transpose32(a);
+
+	// ---- stores: neighbouring lanes swap one word per pair of rows, so that a lane holds 8 bytes of one row -------------------
+	// a[j] is word `lane` of row 32 · warp + j. Even lanes send a[j + 1] and receive the odd neighbour's a[j] (word lane + 1 of
+	// row j); odd lanes the other way round: a warp's store is two sector-aligned 128-byte runs (rows j and j + 1), 8 bytes a lane.
+	u64 const r0(u64(band) * K1H_ROWS + 32 * warp);
+	if (EDGE && r0 >= 64 * R64) return;									// rows are a multiple of 64, sub-tiles of 32: all or nothing
+	unsigned const odd(lane & 1);
+	u64 const X(u64(x) * (K1H_LINES / 8) + 4 * (lane & ~1u));			// byte offset of this lane's 8 bytes in an unshifted run
+	u64 const lineA((r0 + odd) * LB), lineB(lineA + 2 * LB);			// this lane's first two destination lines; 4 · LB is a multiple of 32,
+	u8 *const pA(dst + lineA + X - (lineA & 31));						// so its lines alternate between two sector phases: runs start
+	u8 *const pB(dst + lineB + X - (lineB & 31));						// (line start & 31) bytes early
+	u64 const step(4 * LB);
+#pragma unroll
+	for (int jj = 0; jj < 16; ++jj)
+	{
+		u32 const got(__shfl_xor_sync(0xffffffffu, odd ? a[2 * jj] : a[2 * jj + 1], 1));
+		u32 const lo(odd ? got : a[2 * jj]), hi(odd ? a[2 * jj + 1] : got);
+		u8 *const p(((jj & 1) ? pB : pA) + u64(jj >> 1) * step);
+		if (EDGE)
+		{
+			u64 const line((jj & 1 ? lineB : lineA) + u64(jj >> 1) * step);
+			long long const o((long long) X - (long long) (line & 31));
+			if (o < 0 || u64(o) + 8 > LB) continue;
+		}
+		asm volatile("st.global.v2.u32 [%0], {%1, %2};" :: "l"(p), "r"(lo), "r"(hi) : "memory");
+	}
+}
+
+__global__ void __launch_bounds__(K1_THREADS, 2)
+transpose_bits_sheared_kernel(u64 const * __restrict__ src, u8 * __restrict__ dst, u64 const R64, u64 const C, k1h_shifts const sh)
+{
+	extern __shared__ __align__(16) u64 tile[];
+	u32 const band(blockIdx.x), x(blockIdx.y);
+	bool const edge(0 == x || (u64(x) + 1) * K1H_LINES > C || (u64(band) + 1) * (K1H_ROWS / 64) > R64);
+	if (edge) k1h_tile<true>(src, dst, R64, C, sh, tile, band, x);
+	else k1h_tile<false>(src, dst, R64, C, sh, tile, band, x);
 }
 
 
@@ -328,32 +375,26 @@ int launch_transpose_bits(void const *d_src, u64 rows, u64 cols, void *d_dst, cu
 {
 	if (0 == cols || 0 == rows) return 0;
 	u64 const R64(rows / 64);
-	static int const force([] { char const *env(std::getenv("V2M_K1_TALL")); return env ? std::atoi(env) : -1; }());	// experiments: 0 / 1 / 2 (2: streaming kernel wherever its grid allows)
+	int const force([] { char const *env(std::getenv("V2M_K1_TALL")); return env ? std::atoi(env) : -1; }());	// experiments and tests: 0 / 1 / 2 (2: the sheared kernel wherever its grid allows)
 	{
-		int dev(0), sms(0);
-		V2M_CUDA_TRY(cudaGetDevice(&dev));
-		V2M_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-		u64 const n_bands((rows + K1S_ROWS - 1) / K1S_ROWS), n_tiles((cols + K1S_LINES - 1) / K1S_LINES);
-		u64 const slots(2 * u64(sms));
-		// Long matrices with few row bands (the path matrix as build_variant_graph hands it over: rows = chromosome copies, one
-		// source line per edge): every band of a stretch of lines resident at once, >= 8 tiles per walk.
-		bool const streaming(force >= 0 ? 2 == force && n_bands <= slots : (n_bands <= slots && rows >= 1024 && n_tiles >= 8 * (slots / n_bands)));
-		if (streaming)
+		// The path matrix as build_variant_graph hands it over (rows = chromosome copies, one source line per edge) and anything
+		// of that kind: at least two full row bands and enough lines for the halo not to matter.
+		u64 const n_bands((rows + K1H_ROWS - 1) / K1H_ROWS);
+		u64 const LB(cols / 8);
+		k1h_shifts sh{{0, 0, 0, 0}};
+		for (unsigned j(0); j < 32; ++j) sh.rows[((j * LB) % 32) / 8] |= 1u << j;
+		bool const any_shift(0 != (sh.rows[1] | sh.rows[2] | sh.rows[3]));
+		u64 const n_tiles((LB + (any_shift ? 24 : 0) + 127) / 128);
+		bool const fits(n_tiles <= 65535u && n_bands <= 0x7fffffffu);
+		if (fits && 2 == force)		// opt-in: measured slower than the tile kernels on every shape (see the kernel's header)
 		{
-			u64 const walks_wanted(std::max<u64>(1, slots / n_bands));
-			u32 const walk_tiles(u32((n_tiles + walks_wanted - 1) / walks_wanted));
-			u32 const n_walks(u32((n_tiles + walk_tiles - 1) / walk_tiles));
-			V2M_CUDA_TRY(cudaFuncSetAttribute(transpose_bits_stream_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, K1S_SMEM));
-			transpose_bits_stream_kernel<<<unsigned(n_bands * n_walks), K1_THREADS, K1S_SMEM, stream>>>(
-				static_cast<u64 const *>(d_src), static_cast<u8 *>(d_dst), R64, cols, u32(n_bands), walk_tiles, u32(n_tiles));
-			V2M_CHECK_LAUNCH("transpose_bits_stream_kernel");
+			V2M_CUDA_TRY(cudaFuncSetAttribute(transpose_bits_sheared_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, K1H_SMEM));
+			transpose_bits_sheared_kernel<<<dim3(unsigned(n_bands), unsigned(n_tiles)), K1_THREADS, K1H_SMEM, stream>>>(
+				static_cast<u64 const *>(d_src), static_cast<u8 *>(d_dst), R64, cols, sh);
+			V2M_CHECK_LAUNCH("transpose_bits_sheared_kernel");
 			return 0;
 		}
 	}
-	// Measured (scripts/bench_transpose.py, V2M_K1_TALL=0/1): the tall tiles win when the matrix has at most 512 rows (their
-	// 512-bit band wastes less of a short line: 64 × 4,096,000 runs 2.6 × faster) and when destination lines are an odd
-	// multiple of 8 bytes long (5056 × 3,000,000: 68 % against 61 % of the copy peak); they lose 6 points on sector-aligned
-	// destination lines (their 64-byte source pieces straddle more sectors) and tie on c5.
 	bool const tall(force >= 0 ? 1 == force : (rows <= 512 || 0 != (cols / 8) % 16));
 	if (tall)
 	{
