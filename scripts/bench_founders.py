@@ -114,7 +114,9 @@ def main():
 
     # founder rows (K2c + K2a + K2b), device resident
     assigned = m
-    rows_assigned = np.concatenate([np.full((n_seg, 1), v2m.PLOIDY_MAX, np.uint32), assigned], axis=1)
+    rows_assigned = np.empty((n_seg, 1 + assigned.shape[1]), np.uint32, order="F")     # column-major like lb::matrix
+    rows_assigned[:, 0] = v2m.PLOIDY_MAX
+    rows_assigned[:, 1:] = assigned
     plan = None
     for _ in range(args.iters):                # best of iters, like the two calls above (the host side of this box is noisy)
         if plan is not None:

@@ -15,6 +15,16 @@ from oracle import oracle as orc
 
 pytestmark = pytest.mark.gpu
 
+# The rows compared byte for byte with the oracle at full size are a few fixed points (first / last chromosome copy, …) plus a
+# random sample that changes from round to round: V2M_TEST_SEED overrides the round's seed.
+SAMPLE_SEED = int(os.environ.get("V2M_TEST_SEED", "2"))
+
+
+def _sampled_copies(fixed, H, n_random):
+    rng = np.random.default_rng(SAMPLE_SEED)
+    extra = [int(x) for x in rng.choice(H, n_random, replace=False)]
+    return sorted(set(fixed) | set(extra))
+
 
 @pytest.fixture(scope="module")
 def v2m():
@@ -128,7 +138,7 @@ def test_c2_sampled_rows_vs_oracle_and_row_properties(v2m, c2):
     H, A = g.total_chromosome_copies(), g.aligned_length()
     assert H == 5008
     We = g.e_pad // 64
-    sample = [0, 1, 777, 2503, 4096, 5007]
+    sample = _sampled_copies([0, 1, 5007], H, 4)
     ce_all = dg.paths_by_chrom_copy_and_edge()
     ce = np.zeros_like(ce_all)
     for h in sample:
@@ -199,6 +209,62 @@ def test_c3_cut_positions_matchings_and_founder_rows(v2m, c2):
             hp.close()
 
 
+def test_c3_prefix_founders_vs_oracle_with_default_chunks(v2m, c2):
+    """Founder mode against the oracle at scale: the first ~50,000 ALT edges of the c2 graph with all 5,008 chromosome copies,
+    K4 and K3 with their default chunk count (one per SM), i.e. ~340 columns per chunk and every chunk boundary composed from
+    the chunk-local orders. Cut positions, score, the class data of every cut (representatives, distinct counts, first class,
+    first-is-REF, joined runs in permutation order) and assigned_samples must equal what the reference's sequential pBWT
+    sweep produces (find_cut_positions.cc:93-211, founder_sequence_greedy_output.cc:154-512). ~40 s of CPU for the oracle."""
+    from vcf2multialign_b200._lib import check, lib, ptr
+    w, dg, d_paths = c2
+    g = w.graph
+    Wh = g.h_pad // 64
+    # cut the graph at a node no ALT edge spans (sites of the synthetic workloads do not overlap), ~50,000 edges in
+    csum = g.alt_edge_count_csum.astype(np.int64)
+    tgt = g.alt_edge_targets.astype(np.int64)
+    node = int(np.searchsorted(csum, 50_000))
+    reach = np.maximum.accumulate(tgt)
+    while csum[node] > 0 and reach[csum[node] - 1] > node:
+        node += 1
+    e_cpu = int(csum[node])
+    assert 50_000 <= e_cpu < 51_000
+    e_pad = (e_cpu + 63) // 64 * 64
+    sub = np.zeros(e_pad * Wh, np.uint64)
+    check(lib().v2m_cuda_memcpy_d2h(ptr(sub), d_paths, e_cpu * Wh * 8))
+    N2 = node + 1
+    arrays = dict(
+        reference_positions=g.reference_positions[:N2], aligned_positions=g.aligned_positions[:N2], alt_edge_targets=g.alt_edge_targets[:e_cpu],
+        alt_edge_count_csum=np.concatenate([g.alt_edge_count_csum[:N2], [e_cpu]]).astype(np.uint64), label_offsets=g.label_offsets[: e_cpu + 1],
+        label_chars=g.label_chars[: int(g.label_offsets[e_cpu])], paths_ec=sub, paths_ce=None, h_pad=g.h_pad, e_pad=e_pad,
+        ploidy_csum=g.ploidy_csum, sample_names=g.sample_names)
+    ref = w.ref[: int(g.reference_positions[node]) + 1]
+    og = orc.Graph.from_arrays(dict(arrays, ref=ref))
+    pdg = v2m.DeviceGraph(v2m.VariantGraph.from_arrays(arrays), ref)
+    try:
+        for min_distance, founders in ((50, 25), (0, 7)):
+            f = orc.FounderOutput(og)
+            assert f.find_cut_positions(min_distance)
+            cuts, score = pdg.find_cut_positions(min_distance)
+            t = pdg.last_cut_positions_timing()
+            assert t["chunks"] > 100, t                                  # the default chunking, not a single chunk
+            assert cuts.tolist() == f.cut_positions().tolist() and score == f.score(), min_distance
+            assert f.find_matchings(founders)
+            if min_distance:                                             # the class data of ~25,000 cuts is ~0.5 GB on either side: once is enough
+                rec = f.recorded_classes()
+                got = pdg.segment_classes(cuts)
+                assert len(got) == len(rec) == cuts.size - 1
+                for i, (a, b) in enumerate(zip(got, rec)):
+                    assert (a["distinct"], a["first_class"], a["first_is_ref"]) == (b["distinct"], b["first_class"], b["first_is_ref"]), (min_distance, i)
+                    assert np.array_equal(a["rhs_eq"], b["rhs_eq"]), (min_distance, i)
+                    if i >= 1:
+                        assert np.array_equal(a["joined"], b["joined"]), (min_distance, i)
+                del rec, got
+            m = pdg.find_matchings(cuts, founders)
+            assert np.array_equal(m, f.assigned_samples()), min_distance
+    finally:
+        pdg.close()
+
+
 # ---- c4: the chr1 shape (249 Mbp, 6.3 M ALT edges, 5,008 chromosome copies; 1.25 TB of rows) ----------------------------------
 def test_c4_sampled_rows_vs_oracle(v2m):
     """BASELINE.json's target shape: sampled rows byte for byte against the oracle, plus the row properties of the c2 test."""
@@ -215,7 +281,7 @@ def test_c4_sampled_rows_vs_oracle(v2m):
         synth.path_bits_device(w, d_paths)
         dg = v2m.DeviceGraph(g, w.ref, d_paths_by_edge_and_chrom_copy=d_paths)
         We = g.e_pad // 64
-        sample = [3, 2504, 5007]
+        sample = _sampled_copies([5007], H, 2)
         ce_all = dg.paths_by_chrom_copy_and_edge()
         ce = np.zeros_like(ce_all)
         for h in sample:

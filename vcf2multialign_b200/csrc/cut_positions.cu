@@ -433,6 +433,16 @@ int find_cut_positions_host(graph_holder const &gh, u64 const min_distance, std:
 			cap = (cap < 512 && g.H + 1 > 512) ? 512 : g.H + 1;
 		}
 		V2M_CUDA_TRY(cudaDeviceSynchronize());
+		{
+			// The states at the chunk boundaries stay with the graph for find_matchings (device_graph.hh: sweep_states).
+			std::lock_guard<std::mutex> const lock(gh.sweep_mutex);
+			gh.sweep.clear();
+			gh.sweep.edges.resize(n_chunks);
+			for (u32 j(0); j < n_chunks; ++j) gh.sweep.edges[j] = cut_edges[chunk_cut[j]];
+			gh.sweep.perm = static_cast<unsigned short *>(d_bperm.release());
+			gh.sweep.div = static_cast<u32 *>(d_bdiv.release());
+			gh.sweep.Hp = Hp;
+		}
 		cudaEventElapsedTime(&timing.ms_local, ev[0], ev[1]);
 		cudaEventElapsedTime(&timing.ms_compose, ev[1], ev[2]);
 		cudaEventElapsedTime(&timing.ms_lists, ev[2], ev[3]);

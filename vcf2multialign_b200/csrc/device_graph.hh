@@ -21,6 +21,7 @@
 //   ref_tile_edges ⌈ref_end / K2_TCOL⌉ × uint2         tile_edges in reference coordinates (--unaligned)
 #pragma once
 
+#include <mutex>
 #include <vector>
 
 #include <cuda_runtime.h>
@@ -79,6 +80,7 @@ struct device_plan
 
 int launch_transpose_bits(void const *d_src, u64 rows, u64 cols, void *d_dst, cudaStream_t stream);
 int launch_build_template(device_graph const &g, cudaStream_t stream);
+int launch_check_assigned(u32 const *d_assigned, u64 n, u32 H, u32 *d_bad, cudaStream_t stream);
 int launch_compose_founders(device_graph const &g, u64 const *d_cut_edges, u64 n_segments, u32 const *d_assigned, u32 n_founders, u64 *d_out, cudaStream_t stream);
 int launch_resolve_rows(device_graph const &g, u64 const *d_lines, u32 const *d_line_idx, u32 n_rows, u64 *d_taken, cudaStream_t stream);
 int launch_emit_rows(device_graph const &g, u64 const *d_taken, u32 row_begin, u32 row_end, u64 col_begin, u64 col_end,
@@ -90,15 +92,32 @@ int launch_emit_unaligned(device_graph const &g, u64 const *d_taken, int const *
 
 // What a v2m_graph_t points to: the device arrays plus host copies of the small node / edge arrays the host-side halves
 // need (alt_edge_count_csum: node id → first edge index; aligned_positions and alt_edge_targets: candidate cut positions).
+// The pBWT state (permutation, divergence) before a set of edge columns, left behind by the last find_cut_positions on the
+// graph (its chunk boundaries after pass B): find_matchings on the same graph starts its chunks from these states instead of
+// running the chunk-local sweep and the boundary composition again (the reference, too, sweeps the same columns twice:
+// find_cut_positions.cc:170-176 and founder_sequence_greedy_output.cc:461-469).
+struct sweep_states
+{
+	std::vector<u32>	edges;				// ascending edge indices, edges[0] = 0
+	unsigned short		*perm{};			// [edges.size()][Hp]
+	u32					*div{};				// [edges.size()][Hp]
+	u32					Hp{};
+
+	void clear() { cudaFree(perm); cudaFree(div); perm = nullptr; div = nullptr; edges.clear(); Hp = 0; }
+};
+
 struct graph_holder
 {
 	device_graph		g;
 	std::vector<u64>	csum;
 	std::vector<u64>	alnpos;
 	std::vector<u64>	targets;
+	mutable std::mutex	sweep_mutex;
+	mutable sweep_states sweep;
 
 	~graph_holder()
 	{
+		sweep.clear();
 		cudaFree(g.edge_simple); cudaFree(g.edge_sibling); cudaFree(g.ref); cudaFree(g.refpos); cudaFree(g.alnpos); cudaFree(g.edge_src); cudaFree(g.edge_tgt);
 		cudaFree(g.edges); cudaFree(g.label_chars); cudaFree(g.paths_eh); cudaFree(g.paths_he);
 		cudaFree(g.tmpl); cudaFree(g.tile_edges); cudaFree(g.tile_labels); cudaFree(g.edge_ref); cudaFree(g.ref_tile_edges);

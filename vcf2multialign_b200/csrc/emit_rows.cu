@@ -85,6 +85,20 @@ build_template_kernel(u8 const * __restrict__ ref, u32 const * __restrict__ refp
 // ---------------------------------------------------------------------------------------------------------
 // Founder path bits
 // ---------------------------------------------------------------------------------------------------------
+// assigned_samples entries must be chromosome copies of the graph or PLOIDY_MAX (founder_sequence_greedy_output.cc:170-172).
+__global__ void __launch_bounds__(256)
+check_assigned_kernel(u32 const * __restrict__ assigned, u64 const n, u32 const H, u32 * __restrict__ bad)
+{
+	u64 const stride(u64(gridDim.x) * blockDim.x);
+	bool any(false);
+	for (u64 i(u64(blockIdx.x) * blockDim.x + threadIdx.x); i < n; i += stride)
+	{
+		u32 const v(assigned[i]);
+		any |= PLOIDY_MAX != v && v >= H;
+	}
+	if (any) *bad = 1;
+}
+
 // out line f, word w = OR over segments s intersecting edges [64w, 64w + 64) of
 // (line assigned(s, f) of the copy-major path matrix, word w) & mask(segment edge range).
 __global__ void __launch_bounds__(256)
@@ -567,6 +581,14 @@ int launch_build_template(device_graph const &g, cudaStream_t stream)
 	if (0 == threads) return 0;
 	build_template_kernel<<<unsigned((threads + 255) / 256), 256, 0, stream>>>(g.ref, g.refpos, g.alnpos, g.N, g.A, g.A_alloc, g.tmpl);
 	V2M_CHECK_LAUNCH("build_template_kernel");
+	return 0;
+}
+
+int launch_check_assigned(u32 const *d_assigned, u64 n, u32 H, u32 *d_bad, cudaStream_t stream)
+{
+	if (0 == n) return 0;
+	check_assigned_kernel<<<unsigned(std::min<u64>((n + 255) / 256, 148 * 8)), 256, 0, stream>>>(d_assigned, n, H, d_bad);
+	V2M_CHECK_LAUNCH("check_assigned_kernel");
 	return 0;
 }
 

@@ -211,6 +211,11 @@ namespace {
 				k3_compose_kernel<KW><<<1, K3_THREADS, smem, stream>>>(P);
 				V2M_CHECK_LAUNCH("k3_compose_kernel");
 				break;
+			case 3:
+				V2M_CUDA_TRY(cudaFuncSetAttribute(k3_seed_kernel<KW>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+				k3_seed_kernel<KW><<<n_ctas, K3_THREADS, smem, stream>>>(P);
+				V2M_CHECK_LAUNCH("k3_seed_kernel");
+				break;
 			default:
 				V2M_CUDA_TRY(cudaFuncSetAttribute(k3_emit_kernel<KW>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
 				k3_emit_kernel<KW><<<n_ctas, K3_THREADS, smem, stream>>>(P);
@@ -293,6 +298,37 @@ int segment_classes_host(graph_holder const &gh, u64 const *cut_positions, u64 c
 		}
 		chunk_cut.push_back(u32(n_seg));
 	}
+	// States left behind by find_cut_positions on this graph: chunks then start at the first cut at or after each of them, and
+	// a short sweep from the known state to that cut replaces passes A and B (on c3 cuts are a few columns apart).
+	std::vector<u32> seed_src, seed_edge;
+	dev_buf d_seed_perm, d_seed_div, d_seed_src, d_seed_edge;
+	{
+		std::lock_guard<std::mutex> const lock(gh.sweep_mutex);
+		bool const wanted(max_chunks <= 0 && !std::getenv("V2M_K3_CHUNKS") && !std::getenv("V2M_K3_NO_SEED"));
+		if (wanted && gh.sweep.Hp == Hp && gh.sweep.edges.size() > 1)
+		{
+			std::vector<u32> cc{0}, src{0}, edge{0};
+			for (u32 j(1); j < gh.sweep.edges.size(); ++j)
+			{
+				u32 const e(gh.sweep.edges[j]);
+				u64 const c(std::lower_bound(cut_edges.begin(), cut_edges.end(), e) - cut_edges.begin());
+				if (c >= n_seg) break;
+				if (c == cc.back()) { if (cc.size() > 1) { src.back() = j; edge.back() = e; } continue; }	// a closer state for the same cut
+				cc.push_back(u32(c)); src.push_back(j); edge.push_back(e);
+			}
+			if (cc.size() > 1)
+			{
+				cc.push_back(u32(n_seg));
+				chunk_cut = cc; seed_src = src; seed_edge = edge;
+				// private copies: another thread may run find_cut_positions on the graph while this call is in flight
+				u64 const n(gh.sweep.edges.size());
+				if (d_seed_perm.alloc(n * Hp * 2) || d_seed_div.alloc(n * Hp * 4)) return V2M_ERR_CUDA;
+				V2M_CUDA_TRY(cudaMemcpy(d_seed_perm.p, gh.sweep.perm, n * Hp * 2, cudaMemcpyDeviceToDevice));
+				V2M_CUDA_TRY(cudaMemcpy(d_seed_div.p, gh.sweep.div, n * Hp * 4, cudaMemcpyDeviceToDevice));
+			}
+		}
+	}
+	bool const seeded(!seed_src.empty());
 	u32 const n_chunks(u32(chunk_cut.size() - 1));
 
 	dev_buf d_chunk_cut, d_cut_edges, d_cls, d_classdiv, d_ncls, d_bperm, d_bdiv, d_rhs, d_distinct, d_first, d_isref, d_jcount, d_joined, d_jbase;
@@ -316,11 +352,27 @@ int segment_classes_host(graph_holder const &gh, u64 const *cut_positions, u64 c
 	cudaEvent_t ev[4];
 	for (auto &e : ev) V2M_CUDA_TRY(cudaEventCreate(&e));
 	struct ev_guard { cudaEvent_t *e; ~ev_guard() { for (int i(0); i < 4; ++i) cudaEventDestroy(e[i]); } } const guard{ev};
+	if (seeded)
+	{
+		if (d_seed_src.alloc(seed_src.size() * 4) || d_seed_edge.alloc(seed_edge.size() * 4)) return V2M_ERR_CUDA;
+		V2M_CUDA_TRY(cudaMemcpy(d_seed_src.p, seed_src.data(), seed_src.size() * 4, cudaMemcpyHostToDevice));
+		V2M_CUDA_TRY(cudaMemcpy(d_seed_edge.p, seed_edge.data(), seed_edge.size() * 4, cudaMemcpyHostToDevice));
+		kp.seed_perm = d_seed_perm.as<unsigned short>(); kp.seed_div = d_seed_div.as<u32>();
+		kp.seed_src = d_seed_src.as<u32>(); kp.seed_edge = d_seed_edge.as<u32>();
+	}
 	cudaEventRecord(ev[0], nullptr);
-	if (n_chunks > 1)
-		if (int const st = k3_dispatch(KW, 0, kp, n_chunks - 1, smem, nullptr)) return st;
-	cudaEventRecord(ev[1], nullptr);
-	if (int const st = k3_dispatch(KW, 1, kp, 1, smem, nullptr)) return st;
+	if (seeded)
+	{
+		if (int const st = k3_dispatch(KW, 3, kp, n_chunks, smem, nullptr)) return st;
+		cudaEventRecord(ev[1], nullptr);
+	}
+	else
+	{
+		if (n_chunks > 1)
+			if (int const st = k3_dispatch(KW, 0, kp, n_chunks - 1, smem, nullptr)) return st;
+		cudaEventRecord(ev[1], nullptr);
+		if (int const st = k3_dispatch(KW, 1, kp, 1, smem, nullptr)) return st;
+	}
 	cudaEventRecord(ev[2], nullptr);
 
 	// Joined triples go to per-chunk regions of a pool; a first guess of 48 per cut + H per chunk, exact sizes on a retry.

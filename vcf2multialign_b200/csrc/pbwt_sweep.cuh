@@ -175,6 +175,11 @@ struct k3_params
 	// pass B → C
 	unsigned short	*bperm;			// [n_chunks][Hp] state at the start of every chunk
 	u32				*bdiv;			// [n_chunks][Hp]
+	// k3_seed_kernel (instead of passes A and B): known states to start from
+	unsigned short const	*seed_perm;	// [·][Hp]
+	u32 const		*seed_div;
+	u32 const		*seed_src;		// [n_chunks] which of them chunk j starts from (chunk 0: none, the identity)
+	u32 const		*seed_edge;		// [n_chunks] the edge column that state stands before
 	// pass C outputs (indexed by cut - 1)
 	u32				*rhs_eq;		// optional [n_cuts - 1][H]
 	u32				*distinct;
@@ -371,6 +376,41 @@ k3_compose_kernel(k3_params const P)
 
 
 // ---------------------------------------------------------------------------------------------------------
+// Instead of passes A and B: the state at every chunk boundary from a known state at or before it
+// ---------------------------------------------------------------------------------------------------------
+template <int KW>
+__global__ void __launch_bounds__(K3_THREADS, 1)
+k3_seed_kernel(k3_params const P)
+{
+	extern __shared__ __align__(128) u8 k3_raw[];
+	k3_smem const s(k3_carve(k3_raw, P.Hp, P.Wh));
+	k3_state const st(k3_make_state(s, P.H));
+	u32 const j(blockIdx.x);
+	unsigned short *bperm(P.bperm + u64(j) * P.Hp);
+	u32 *bdiv(P.bdiv + u64(j) * P.Hp);
+	if (0 == j)
+	{
+		for (u32 i(threadIdx.x); i < P.Hp; i += K3_THREADS) { bperm[i] = (unsigned short) i; bdiv[i] = 0; }		// as pass B starts (pbwt.hh:61-74)
+		return;
+	}
+	u32 const eb(P.seed_edge[j]), ee(P.cut_edges[P.chunk_cut[j]]);
+	{
+		unsigned short const *sp(P.seed_perm + u64(P.seed_src[j]) * P.Hp);
+		u32 const *sd(P.seed_div + u64(P.seed_src[j]) * P.Hp);
+		for (u32 i(threadIdx.x); i < P.Hp; i += K3_THREADS) { s.perm[i] = sp[i]; s.div[i] = sd[i]; }
+	}
+	__syncthreads();
+	if (ee > eb)
+	{
+		k3_cols_begin(P, s, eb, ee);
+		k3_sweep<KW>(P, s, st, eb, ee, [](u32){}, [](u32, u32){});
+	}
+	for (u32 i(threadIdx.x); i < P.Hp; i += K3_THREADS) { bperm[i] = s.perm[i]; bdiv[i] = s.div[i]; }
+}
+
+
+
+// ---------------------------------------------------------------------------------------------------------
 // Host helpers shared by the drivers
 // ---------------------------------------------------------------------------------------------------------
 struct dev_buf
@@ -384,6 +424,7 @@ struct dev_buf
 		return 0;
 	}
 	template <typename T> T *as() const { return static_cast<T *>(p); }
+	void *release() { void *q(p); p = nullptr; return q; }
 };
 
 

@@ -228,7 +228,7 @@ transpose_bits_tall_kernel(u64 const * __restrict__ src, u32 * __restrict__ dst,
 //       The tile loads a halo of 192 source lines (L2 hits: the neighbouring tile's CTA reads them as its own at the same
 //       time) and the sub-tile read costs up to four LDS + three LOP3 per word instead of one LDS;
 //   RESULT (profiles/r02_k1_sheared.txt): correct on every shape (tests/test_gpu_parity.py runs all three kernels against the
-//   oracle) and indifferent to the destination lines' phase, as intended — but 1.85 ms on c5 against the tile kernel's 1.57,
+//   CPU restatement) and indifferent to the destination lines' phase, as intended — but 1.85 ms on c5 against the tile kernel's 1.57,
 //   2.19 against 1.73 (tall) on the c4 shape, 1.74 against 1.43 on a sector-aligned shape. ncu: the ALU pipe is 71 % busy and
 //   `math pipe throttle` is the top stall (1.16 G warp instructions against the tile kernel's 0.77 G): with the stores out of
 //   the way the transpose is bound by its own integer work — 64 PRMT + 144 LOP3 / SHF for the bit stages plus index

@@ -116,7 +116,7 @@ class DeviceGraph:
         m = np.asarray(assigned_samples, dtype=np.uint32)
         if m.ndim != 2 or m.shape[0] != cuts.size - 1:
             raise V2MError("assigned_samples must be segments × founders with segments = len(cut_positions) - 1")
-        flat = np.ascontiguousarray(m.T).reshape(-1)
+        flat = np.asfortranarray(m).T.reshape(-1)              # no copy when m is column-major already (find_matchings returns it so)
         p = C.c_void_p()
         check(lib().v2m_cuda_plan_founders(self._h, ptr(cuts), cuts.size - 1, ptr(flat), m.shape[1], C.byref(p)))
         return Plan(self, p)
@@ -131,7 +131,7 @@ class DeviceGraph:
         check(lib().v2m_cuda_find_matchings(self._h, ptr(cuts), cuts.size, founder_count, int(keep_ref_edges), ptr(assigned), C.byref(found)))
         if not found.value:
             return None
-        return assigned[: n_seg * founder_count].reshape(founder_count, n_seg).T.copy()
+        return assigned[: n_seg * founder_count].reshape(founder_count, n_seg).T          # column-major like lb::matrix: plan_founders takes it as is
 
     def find_cut_positions(self, min_distance: int = 0):
         """find_initial_cut_positions_lambda_min (find_cut_positions.cc:93-211): K4 on the device, recurrence + trace-back on
