@@ -329,12 +329,16 @@ emit_rows_kernel(emit_params const p)
 	// ---- staging warp: template tile, edge records and labels of the units, one unit ahead of the rows ------------------
 	if (K2P_CWARPS == warp)
 	{
-		// One unit ahead of itself: the ticket and the tile's edge range of unit k + 1 are asked for while the words of unit k
-		// are on their way, so that the warp spends one memory latency per unit, not three.
-		auto const next_ticket([&]() -> u32 { return __shfl_sync(0xffffffffu, 0 == lane ? atomicAdd(p.tickets, 1u) : 0u, 0); });
+		// Two units ahead of itself: the ticket of unit k + 2 is drawn (one lane's atomic, its result not looked at) while unit
+		// k is staged, and the edge / label ranges of unit k + 1 are loaded while the words of unit k are on their way. The warp
+		// then waits for one memory round trip per unit — the gather — instead of three (ticket, label range, gather), which is
+		// what bounds launches of a few rows: their units are too short for the row warps to hide the staging behind.
+		auto const draw_ticket([&]() -> u32 { return 0 == lane ? atomicAdd(p.tickets, 1u) : 0u; });
 		auto const edges_of([&](u32 const u) -> uint2 { return u < n_units ? p.tile_edges[p.first_tile + u / p.n_row_chunks] : make_uint2(0, 0); });
-		u32 unit(next_ticket());
-		uint2 te(edges_of(unit));
+		auto const labels_of([&](u32 const u) -> uint2 { return u < n_units ? p.tile_labels[p.first_tile + u / p.n_row_chunks] : make_uint2(0, 0); });
+		u32 unit(__shfl_sync(0xffffffffu, draw_ticket(), 0));
+		u32 ticket_after(draw_ticket());				// lane 0: the unit after `unit`; read at the top of the next iteration
+		uint2 te(edges_of(unit)), tl(labels_of(unit));
 #pragma unroll 1
 		for (u32 k(0); ; ++k)
 		{
@@ -350,14 +354,12 @@ emit_rows_kernel(emit_params const p)
 				}
 				break;
 			}
-			u32 const unit_after(next_ticket());
 			u64 const tile(p.first_tile + unit / p.n_row_chunks);
 			u64 const w_lo(te.x / 64);
 			u32 const n_words(te.y != te.x ? u32((te.y - 1) / 64 - w_lo + 1) : 0);
 			bool const words_staged(n_words <= K2P_WORDS);
 			if (0 == lane)
 			{
-				uint2 const tl(p.tile_labels[tile]);
 				u32 const n_e(te.y - te.x);
 				u32 const lab_base(tl.x & ~15u);										// bulk copies start at 16-byte boundaries
 				u32 const lab_bytes(tl.y > tl.x ? ((tl.y - lab_base + 15u) & ~15u) : 0);
@@ -385,7 +387,9 @@ emit_rows_kernel(emit_params const p)
 					got[j] = (rb0 + row < rb1 && i < n_words) ? p.taken[u64(rb0 + row) * p.We + w_lo + i] : 0;
 				}
 			}
-			uint2 const te_after(edges_of(unit_after));
+			u32 const unit_after(__shfl_sync(0xffffffffu, ticket_after, 0));	// drawn one iteration ago
+			ticket_after = draw_ticket();
+			uint2 const te_after(edges_of(unit_after)), tl_after(labels_of(unit_after));
 			if (gather)
 			{
 #pragma unroll
@@ -398,7 +402,7 @@ emit_rows_kernel(emit_params const p)
 			__syncwarp();
 			if (0 == lane) mbar_arrive(&sm.full[s]);		// release: the header and the words are visible to the waiters
 			unit = unit_after;
-			te = te_after;
+			te = te_after; tl = tl_after;
 		}
 		return;
 	}
