@@ -93,7 +93,14 @@ int v2m_cuda_transpose_bits(const uint64_t *src, uint64_t rows, uint64_t cols, u
 int v2m_cuda_transpose_bits_device(const void *d_src, uint64_t rows, uint64_t cols, void *d_dst, void *stream);
 
 /* --- graph residency ------------------------------------------------------------------------------------- */
+/* view->ref_seq may be NULL: the graph then serves the sweeps (v2m_cuda_find_cut_positions, v2m_cuda_find_matchings,
+ * v2m_cuda_segment_classes — the reference's find_cut_positions(graph, …) / find_matchings(graph, …) take no reference
+ * sequence either, include/vcf2multialign/output.hh:123,126) and plans; calls that produce rows return V2M_ERR_STATE until
+ * v2m_cuda_graph_attach_reference has supplied it. */
 int v2m_cuda_graph_upload(const v2m_graph_view *view, v2m_graph_t *out);
+/* Uploads the reference sequence of a graph that was uploaded without one and builds the REF-aligned template; a no-op when
+ * the graph has it already. */
+int v2m_cuda_graph_attach_reference(v2m_graph_t g, const char *ref_seq, uint64_t ref_len);
 int v2m_cuda_graph_free(v2m_graph_t g);
 int v2m_cuda_graph_aligned_length(v2m_graph_t g, uint64_t *out);   /* aligned_positions.back() */
 /* Copy-major path words as resident on the device (rows = e_pad, cols = h_pad): lets callers fetch the K1 result
@@ -162,6 +169,13 @@ int v2m_cuda_write_a2m(v2m_plan_t p, const char *ids, int unaligned, int fd, v2m
 typedef int (*v2m_sink)(const void *bytes, uint64_t n, void *ctx);
 int v2m_cuda_stream_a2m(v2m_plan_t p, const char *ids, int unaligned, v2m_sink sink, void *sink_ctx, v2m_row_callback row_done, void *ctx);
 
+/* The rows alone — what haplotype_output::output_separate / output::output_sequence_file (libvcf2multialign/output.cc:18-44)
+ * write one file or --pipe subprocess per row from: sink(row, bytes, n, ctx) is called once per row of the plan, in row
+ * order, from the calling thread, with the row's bytes in a pinned buffer that is reused after the call returns. Same block
+ * pipeline as v2m_cuda_stream_a2m (the next block is produced and copied while the sink consumes this one). */
+typedef int (*v2m_row_sink)(uint32_t row, const void *bytes, uint64_t n, void *ctx);
+int v2m_cuda_stream_rows(v2m_plan_t p, int unaligned, v2m_row_sink sink, void *sink_ctx);
+
 /* --- K3: per-cut haplotype classes for founder_sequence_greedy_output::find_matchings
  *         (libvcf2multialign/founder_sequence_greedy_output.cc:213-253, 460-469; pbwt.hh:77-134) ----------- */
 /* cut_positions: n_cuts node ids as in founder_sequence_greedy_output::cut_positions() (first 0, last the sink). Every
@@ -175,7 +189,10 @@ int v2m_cuda_stream_a2m(v2m_plan_t p, const char *ids, int unaligned, v2m_sink s
  *   joined triples (lhs_rep, rhs_rep, size) in permutation order: joined_offsets[c-1] … joined_offsets[c] index into joined
  *   (for c = 1 the lhs is V2M_PLOIDY_MAX: the single-segment case of :474-509). joined holds joined_cap triples; if that is
  *   too small the call returns V2M_ERR_ARGUMENT with the needed count in joined_offsets[n_cuts-1].
- * At most 8192 chromosome copies (the sweep keeps the pBWT state in shared memory). */
+ * LIMIT: at most 8192 chromosome copies — the sweep keeps the pBWT state (permutation as 16-bit positions, divergence) of all
+ * copies in one CTA's shared memory; the reference's pbwt_context (include/vcf2multialign/pbwt.hh:61-74) has no such limit.
+ * 1000 Genomes phase 3 (5,008 copies) fits; 1000G + HGDP (~8,400) or larger cohorts do not and get V2M_ERR_ARGUMENT from the
+ * three founder-mode calls (K3, find_matchings, find_cut_positions). Row emission has no such limit. */
 int v2m_cuda_segment_classes(v2m_graph_t g, const uint64_t *cut_positions, uint64_t n_cuts,
                              uint32_t *rhs_eq, uint32_t *distinct, uint32_t *first_class, uint8_t *first_is_ref,
                              uint64_t *joined_offsets /* [n_cuts] */, uint32_t *joined, uint64_t joined_cap);

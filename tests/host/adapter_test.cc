@@ -10,6 +10,7 @@
 
 #include "../../oracle/v2m_oracle.hh"
 #include "../../vcf2multialign_b200/host/v2m_b200.hh"
+#include "../../vcf2multialign_b200/host/v2m_cereal.hh"
 
 namespace orc = v2m_oracle;
 namespace b200 = v2m_b200;
@@ -113,6 +114,26 @@ int main(int argc, char **argv)
 			expect(ss.str() == sink.s, std::string("output_sequence") + (unaligned ? " --unaligned" : ""));
 		}
 
+		// output_sequence, the lb::file_handle & overload (sequence_writer.hh:48-56) that output::output_sequence_file calls
+		for (bool const unaligned : {false, true})
+		{
+			orc::u32 const copy(og.total_chromosome_copies() / 2);
+			orc::string_sink sink; orc::sequence_writing_delegate od(copy);
+			orc::output_sequence(ref_seq, og, sink, "row.a2m", unaligned, od);
+			std::string const dst(scratch + "/one_row_" + std::to_string(unaligned));
+			{
+				b200::file_handle handle(::open(dst.c_str(), O_WRONLY | O_CREAT | O_EXCL, 0644));
+				b200::sequence_writing_delegate d(copy);
+				b200::output_sequence(ref_seq, graph, handle, "row.a2m", unaligned, d);
+				b200::sequence_writing_delegate dref;						// PLOIDY_MAX: the REF row, appended to the same descriptor
+				b200::output_sequence(ref_seq, graph, handle, nullptr, unaligned, dref);
+			}
+			orc::sequence_writing_delegate oref;
+			orc::output_sequence(ref_seq, og, sink, nullptr, unaligned, oref);
+			expect(slurp(dst) == sink.s, std::string("output_sequence(file_handle &)") + (unaligned ? " --unaligned" : ""));
+		}
+		b200::release_resident_graph();
+
 		// haplotype_output::output_a2m(stream) with every option combination the CLI has for it
 		for (int mask(0); mask < 8; ++mask)
 		{
@@ -170,6 +191,25 @@ int main(int argc, char **argv)
 			expect(only(del.log.str(), 'S') == only(odel.log.str(), 'S') && only(del.log.str(), 'H').empty(), "  delegate calls");
 		}
 
+		// output_separate through --pipe: one subprocess per row (output.cc:26-38)
+		{
+			log_delegate_oracle odel; orc::haplotype_output oout(nullptr, true, false, odel);
+			orc::named_outputs files; oout.output_separate(ref_seq, og, true, files);
+			std::string const dir(scratch + "/sep_pipe");
+			::mkdir(dir.c_str(), 0755);
+			std::string const script(scratch + "/sink_sep.sh");
+			{ std::ofstream f(script); f << "#!/bin/sh\ncat > \"$1\"\n"; }
+			::chmod(script.c_str(), 0755);
+			char cwd[4096]; if (!::getcwd(cwd, sizeof cwd)) return 2;
+			if (::chdir(dir.c_str())) return 2;
+			log_delegate del; b200::haplotype_output out(script.c_str(), nullptr, true, false, del);
+			out.output_separate(ref_seq, graph, true);
+			bool same(true);
+			for (auto const &[name, bytes] : files) same = same && slurp(name) == bytes;
+			if (::chdir(cwd)) return 2;
+			expect(same && !files.empty() && std::size_t(del.exits) == files.size(), "haplotype_output::output_separate through --pipe");
+		}
+
 		// founder_sequence_greedy_output: find_matchings + output_a2m + output_separate
 		{
 			log_delegate_oracle odel;
@@ -191,6 +231,29 @@ int main(int argc, char **argv)
 				expect(ss.str() == sink.s, "founder_sequence_greedy_output::output_a2m bytes");
 				expect(only(del.log.str(), 'H') == only(odel.log.str(), 'H') && only(del.log.str(), 'S') == only(odel.log.str(), 'S'), "  delegate calls");
 				std::cout << ss.str();
+			}
+			// The reference's own parameter lists (output.hh:121-126): no reference sequence for the two sweeps, the graph stays
+			// resident from find_cut_positions to output_a2m; cut positions through their cereal file.
+			if (have_cuts && oout.m_assigned_samples.data.size())
+			{
+				log_delegate del;
+				b200::founder_sequence_greedy_output out(nullptr, "chrQ", true, false, false, del);
+				expect(out.find_cut_positions(graph, 0), "find_cut_positions(graph, minimum_distance)");
+				expect(out.cut_positions() == oout.m_cut_positions && out.max_segmentation_height() == oout.m_score, "  cut_positions / score identical");
+				std::string const cut_file(scratch + "/cuts.cereal");
+				out.output_cut_positions(cut_file.c_str());
+				b200::founder_sequence_greedy_output other(nullptr, "chrQ", true, false, false, del);
+				other.load_cut_positions(cut_file.c_str());
+				expect(other.cut_positions() == out.cut_positions() && other.max_segmentation_height() == out.max_segmentation_height()
+					&& other.minimum_distance() == 0, "output_cut_positions(path) / load_cut_positions(path) round trip");
+				expect(other.find_matchings(graph, founders), "find_matchings(graph, founder_count) on loaded cut positions");
+				expect(other.assigned_samples().data == oout.m_assigned_samples.data, "  assigned_samples identical");
+				log_delegate_oracle odel2;
+				orc::founder_sequence_greedy_output oout2("chrQ", true, false, false, odel2);
+				oout2.m_cut_positions = oout.m_cut_positions; oout2.m_assigned_samples = oout.m_assigned_samples;
+				orc::string_sink sink; oout2.output_a2m(ref_seq, og, sink);
+				std::ostringstream ss; other.output_a2m(ref_seq, graph, ss);		// the reference sequence arrives only now
+				expect(ss.str() == sink.s, "  output_a2m after the reference-less sweeps");
 			}
 			b200::founder_sequence_greedy_output none(nullptr, nullptr, true, false, false, *new log_delegate);
 			expect(!none.find_matchings(ref_seq, graph, founders), "find_matchings without cut positions returns false");

@@ -839,3 +839,31 @@ def test_shard_graph_rows_on_device(v2m, tmp_path):
                 assert out[i].tobytes() == og.output_sequence(c), (world, rank, c)
             plan.close()
             dg.close()
+
+
+def test_graph_without_reference_serves_the_sweeps(v2m, tmp_path):
+    """find_cut_positions(graph, …) / find_matchings(graph, …) take no reference sequence (output.hh:123, 126): a graph uploaded
+    without one runs both; rows need v2m_cuda_graph_attach_reference first and are then identical."""
+    og = rg.random_oracle_graph(str(tmp_path), 31, ref_len=4000, n_records=400, n_samples=12, ploidy=2)
+    a = dict(og.arrays())
+    a["paths_ce"] = None
+    g = v2m.VariantGraph.from_arrays(a)
+    dg = v2m.DeviceGraph(g, None)
+    f = orc.FounderOutput(og)
+    assert f.find_cut_positions(10)
+    cuts, score = dg.find_cut_positions(10)
+    assert cuts.tolist() == f.cut_positions().tolist() and score == f.score()
+    try:
+        ok = f.find_matchings(3)
+    except orc.OracleError:
+        ok = False
+    if ok:
+        assert np.array_equal(dg.find_matchings(cuts, 3), f.assigned_samples())
+    plan = dg.plan_haplotypes([0, orc.PLOIDY_MAX])
+    with pytest.raises(v2m.V2MError):
+        plan.emit_rows()
+    dg.attach_reference(og.arrays()["ref"])
+    rows = plan.emit_rows()
+    assert rows[0].tobytes() == og.output_sequence(0) and rows[1].tobytes() == og.output_sequence(orc.PLOIDY_MAX)
+    un = plan.emit_rows_unaligned()
+    assert un[0] == og.output_sequence(0, None, True)

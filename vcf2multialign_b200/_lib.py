@@ -39,6 +39,7 @@ class GraphView(C.Structure):
 
 ROW_CALLBACK = C.CFUNCTYPE(None, C.c_uint32, C.c_void_p)
 SINK = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_uint64, C.c_void_p)
+ROW_SINK = C.CFUNCTYPE(C.c_int, C.c_uint32, C.c_void_p, C.c_uint64, C.c_void_p)
 
 # name → (restype, argtypes); every symbol include/v2m_cuda.h declares.
 _vp, _u64, _u32, _i32 = C.c_void_p, C.c_uint64, C.c_uint32, C.c_int
@@ -61,6 +62,7 @@ SYMBOLS = {
     "v2m_cuda_transpose_bits": (_i32, [_vp, _u64, _u64, _vp]),
     "v2m_cuda_transpose_bits_device": (_i32, [_vp, _u64, _u64, _vp, _vp]),
     "v2m_cuda_graph_upload": (_i32, [_vp, _vp]),
+    "v2m_cuda_graph_attach_reference": (_i32, [_vp, _vp, _u64]),
     "v2m_cuda_graph_free": (_i32, [_vp]),
     "v2m_cuda_graph_aligned_length": (_i32, [_vp, _vp]),
     "v2m_cuda_graph_download_paths_by_chrom_copy_and_edge": (_i32, [_vp, _vp]),
@@ -80,6 +82,7 @@ SYMBOLS = {
     "v2m_cuda_emit_rows_unaligned": (_i32, [_vp, _u32, _u32, _vp, _vp]),
     "v2m_cuda_write_a2m": (_i32, [_vp, C.c_char_p, _i32, _i32, ROW_CALLBACK, _vp]),
     "v2m_cuda_stream_a2m": (_i32, [_vp, C.c_char_p, _i32, SINK, _vp, ROW_CALLBACK, _vp]),
+    "v2m_cuda_stream_rows": (_i32, [_vp, _i32, ROW_SINK, _vp]),
     "v2m_cuda_segment_classes": (_i32, [_vp, _vp, _u64, _vp, _vp, _vp, _vp, _vp, _vp, _u64]),
     "v2m_cuda_find_matchings": (_i32, [_vp, _vp, _u64, _u32, _i32, _vp, _vp]),
     "v2m_cuda_last_segment_classes_timing": (_i32, [_vp, _vp]),

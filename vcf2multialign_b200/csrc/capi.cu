@@ -70,6 +70,16 @@ using namespace v2m;
 
 struct v2m_plan_s : v2m::plan_holder {};
 
+// The reference sequence and the REF-aligned template built from it (the bytes of the REF row).
+static int attach_reference(graph_holder &holder, char const *ref_seq, u64 const ref_len)
+{
+	device_graph &g(holder.g);
+	g.L = ref_len;
+	if (int const st = dev_upload(g.ref, reinterpret_cast<u8 const *>(ref_seq), g.L, g.L + 16)) return st;
+	if (int const st = dev_alloc(g.tmpl, g.A_alloc)) return st;
+	return launch_build_template(g, nullptr);
+}
+
 
 extern "C" {
 
@@ -176,15 +186,15 @@ int v2m_cuda_graph_upload(const v2m_graph_view *view, v2m_graph_t *out)
 	if (view->h_pad && view->e_pad && !view->paths_by_edge_and_chrom_copy && !view->paths_by_chrom_copy_and_edge)
 		return fail(V2M_ERR_ARGUMENT, "graph_upload: no path matrix given");
 	u64 const A(view->aligned_positions[N - 1]);
-	if (A >= (u64(1) << 32) - 2 * K2_TCOL || view->ref_len >= (u64(1) << 32))
+	if (A >= (u64(1) << 32) - 2 * K2_TCOL || view->ref_len >= (u64(1) << 32) || view->reference_positions[N - 1] >= (u64(1) << 32))
 		return fail(V2M_ERR_ARGUMENT, "graph_upload: aligned length or reference length does not fit 32-bit device positions");
-	if (view->reference_positions[N - 1] > view->ref_len)
+	if (view->ref_seq && view->reference_positions[N - 1] > view->ref_len)
 		return fail(V2M_ERR_ARGUMENT, "graph_upload: node positions exceed the reference length");
 
 	auto holder(std::make_unique<v2m_graph_s>());
 	device_graph &g(holder->g);
 	V2M_CUDA_TRY(cudaGetDevice(&g.device));
-	g.N = N; g.E = E; g.L = view->ref_len; g.A = A;
+	g.N = N; g.E = E; g.L = view->ref_seq ? view->ref_len : 0; g.A = A;
 	g.h_pad = view->h_pad; g.e_pad = view->e_pad; g.Wh = g.h_pad / 64; g.We = g.e_pad / 64;
 	g.H = view->total_chromosome_copies;
 	g.n_tiles = (A + K2_TCOL - 1) / K2_TCOL;
@@ -262,7 +272,6 @@ int v2m_cuda_graph_upload(const v2m_graph_view *view, v2m_graph_t *out)
 	g.n_ref_tiles = (u64(g.ref_end) + K2_TCOL - 1) / K2_TCOL;
 	std::vector<uint2> const ref_tile_edges(tile_edge_ranges(g.n_ref_tiles, [&edge_ref](u64 e){ return edge_ref[e]; }));
 
-	if (int const st = dev_upload(g.ref, reinterpret_cast<u8 const *>(view->ref_seq), g.L, g.L + 16)) return st;
 	if (int const st = dev_upload(g.refpos, refpos.data(), N)) return st;
 	if (int const st = dev_upload(g.alnpos, alnpos.data(), N)) return st;
 	if (int const st = dev_upload(g.edge_src, edge_src.data(), g.e_pad)) return st;
@@ -299,10 +308,23 @@ int v2m_cuda_graph_upload(const v2m_graph_view *view, v2m_graph_t *out)
 			if (int const st = launch_transpose_bits(g.paths_he, g.e_pad, g.h_pad, g.paths_eh, nullptr)) return st;
 	}
 
-	if (int const st = dev_alloc(g.tmpl, g.A_alloc)) return st;
-	if (int const st = launch_build_template(g, nullptr)) return st;
+	// Without a reference the graph serves the sweeps (find_cut_positions, find_matchings, segment_classes) and plans; rows
+	// need v2m_cuda_graph_attach_reference first.
+	if (view->ref_seq)
+		if (int const st = attach_reference(*holder, view->ref_seq, view->ref_len)) return st;
 	V2M_CUDA_TRY(cudaDeviceSynchronize());
 	*out = holder.release();
+	return V2M_OK;
+}
+
+int v2m_cuda_graph_attach_reference(v2m_graph_t g, const char *ref_seq, uint64_t ref_len)
+{
+	if (!g || !ref_seq) return fail(V2M_ERR_ARGUMENT, "graph_attach_reference: NULL argument");
+	if (g->g.tmpl) return V2M_OK;		// already there: the reference of a graph does not change
+	if (ref_len >= (u64(1) << 32) || g->g.ref_end > ref_len)
+		return fail(V2M_ERR_ARGUMENT, "graph_attach_reference: node positions exceed the reference length (or it does not fit 32-bit device positions)");
+	if (int const st = attach_reference(*g, ref_seq, ref_len)) return st;
+	V2M_CUDA_TRY(cudaDeviceSynchronize());
 	return V2M_OK;
 }
 
@@ -338,6 +360,7 @@ int v2m_cuda_graph_download_path_lines(v2m_graph_t g, uint32_t first_copy, uint3
 int v2m_cuda_graph_download_template(v2m_graph_t g, uint8_t *dst)
 {
 	if (!g || !dst) return fail(V2M_ERR_ARGUMENT, "NULL argument");
+	if (!g->g.tmpl) return fail(V2M_ERR_STATE, "graph_download_template: the graph was uploaded without a reference sequence");
 	V2M_CUDA_TRY(cudaMemcpy(dst, g->g.tmpl, g->g.A, cudaMemcpyDeviceToHost));
 	return V2M_OK;
 }
@@ -446,6 +469,7 @@ int v2m_cuda_plan_download_taken(v2m_plan_t p, uint64_t *dst)
 static int check_emit_args(v2m_plan_t p, uint32_t row_begin, uint32_t row_end, uint64_t col_begin, uint64_t col_end)
 {
 	if (!p) return fail(V2M_ERR_ARGUMENT, "emit_rows: NULL plan");
+	if (!p->p.graph->tmpl) return fail(V2M_ERR_STATE, "emit_rows: the graph was uploaded without a reference sequence (v2m_cuda_graph_attach_reference)");
 	if (row_begin > row_end || row_end > p->p.n_rows) return fail(V2M_ERR_ARGUMENT, "emit_rows: row range out of bounds");
 	if (col_begin > col_end || col_end > p->p.graph->A) return fail(V2M_ERR_ARGUMENT, "emit_rows: column range out of bounds");
 	return V2M_OK;
@@ -598,6 +622,7 @@ int v2m_cuda_plan_row_lengths(v2m_plan_t p, int unaligned, uint64_t *out)
 int v2m_cuda_emit_rows_unaligned(v2m_plan_t p, uint32_t row_begin, uint32_t row_end, const uint64_t *offsets, uint8_t *out)
 {
 	if (!p) return fail(V2M_ERR_ARGUMENT, "emit_rows_unaligned: NULL plan");
+	if (!p->p.graph->ref) return fail(V2M_ERR_STATE, "emit_rows_unaligned: the graph was uploaded without a reference sequence (v2m_cuda_graph_attach_reference)");
 	if (row_begin > row_end || row_end > p->p.n_rows) return fail(V2M_ERR_ARGUMENT, "emit_rows_unaligned: row range out of bounds");
 	if (row_begin == row_end) return V2M_OK;
 	if (!offsets || !out) return fail(V2M_ERR_ARGUMENT, "emit_rows_unaligned: NULL argument");
@@ -709,6 +734,8 @@ namespace {
 		u8		*base{};		// mapping of [map_offset, map_offset + map_bytes) of the file
 		u64		map_offset{}, map_bytes{};
 		u64		position{};		// file offset of the next byte of the stream
+		u64		grown_from{};	// size of the file before it was extended for the stream
+		bool	grown{};
 
 		bool open(int const fd_, u64 const stream_bytes)
 		{
@@ -720,13 +747,20 @@ namespace {
 			if (pos < 0 || 0 == stream_bytes) return false;
 			u64 const page(u64(::sysconf(_SC_PAGESIZE)));
 			u64 const end(u64(pos) + stream_bytes);
-			if (u64(sb.st_size) < end && 0 != ::ftruncate(fd_, off_t(end))) return false;
+			// The blocks of the extended range are allocated up front: a store into a hole of a mapped file on a full disk (or
+			// over quota) raises SIGBUS, where write(2) — the caller's fallback when this returns false — reports ENOSPC.
+			if (u64(sb.st_size) < end)
+			{
+				if (0 != ::posix_fallocate(fd_, sb.st_size, off_t(end) - sb.st_size)) return false;
+				grown_from = u64(sb.st_size); grown = true;
+			}
 			map_offset = u64(pos) / page * page;
 			map_bytes = end - map_offset;
 			void *m(::mmap(nullptr, map_bytes, PROT_READ | PROT_WRITE, MAP_SHARED, fd_, off_t(map_offset)));
 			if (MAP_FAILED == m)
 			{
-				if (u64(sb.st_size) < end) (void) ::ftruncate(fd_, sb.st_size);
+				if (grown) (void) ::ftruncate(fd_, off_t(grown_from));
+				grown = false;
 				return false;
 			}
 			fd = fd_; base = static_cast<u8 *>(m); position = u64(pos);
@@ -740,6 +774,7 @@ namespace {
 			if (!base) return V2M_OK;
 			::munmap(base, map_bytes);
 			base = nullptr;
+			if (!ok && grown) (void) ::ftruncate(fd, off_t(std::max(grown_from, position)));		// keep what was written, drop the rest
 			if (ok && ::lseek(fd, off_t(position), SEEK_SET) < 0) return fail(V2M_ERR_STATE, std::string("lseek failed: ") + std::strerror(errno));
 			return V2M_OK;
 		}
@@ -764,7 +799,8 @@ namespace {
 	}
 }
 
-static int stream_a2m_impl(v2m_plan_t p, const char *ids, int unaligned, v2m_sink sink, void *sink_ctx, v2m_row_callback row_done, void *ctx, int positional_fd);
+static int stream_a2m_impl(v2m_plan_t p, const char *ids, int unaligned, v2m_sink sink, void *sink_ctx, v2m_row_callback row_done, void *ctx, int positional_fd,
+	v2m_row_sink row_sink = nullptr);
 
 
 extern "C" int v2m_cuda_write_a2m(v2m_plan_t p, const char *ids, int unaligned, int fd, v2m_row_callback row_done, void *ctx)
@@ -777,9 +813,17 @@ extern "C" int v2m_cuda_stream_a2m(v2m_plan_t p, const char *ids, int unaligned,
 	return stream_a2m_impl(p, ids, unaligned, sink, sink_ctx, row_done, ctx, -1);
 }
 
-static int stream_a2m_impl(v2m_plan_t p, const char *ids, int unaligned, v2m_sink sink, void *sink_ctx, v2m_row_callback row_done, void *ctx, int const positional_fd)
+extern "C" int v2m_cuda_stream_rows(v2m_plan_t p, int unaligned, v2m_row_sink sink, void *sink_ctx)
 {
-	if (!p || !sink || (!ids && p->p.n_rows)) return fail(V2M_ERR_ARGUMENT, "stream_a2m: NULL argument");
+	if (!sink) return fail(V2M_ERR_ARGUMENT, "stream_rows: NULL sink");
+	return stream_a2m_impl(p, nullptr, unaligned, nullptr, sink_ctx, nullptr, nullptr, -1, sink);
+}
+
+static int stream_a2m_impl(v2m_plan_t p, const char *ids, int unaligned, v2m_sink sink, void *sink_ctx, v2m_row_callback row_done, void *ctx, int const positional_fd,
+	v2m_row_sink const row_sink)
+{
+	if (!p || (!sink && !row_sink) || (!row_sink && !ids && p->p.n_rows)) return fail(V2M_ERR_ARGUMENT, "stream_a2m: NULL argument");
+	if (!p->p.graph->tmpl) return fail(V2M_ERR_STATE, "stream_a2m: the graph was uploaded without a reference sequence (v2m_cuda_graph_attach_reference)");
 	device_graph const &g(*p->p.graph);
 	u32 const n_rows(p->p.n_rows);
 	if (0 == n_rows) return V2M_OK;
@@ -870,6 +914,13 @@ static int stream_a2m_impl(v2m_plan_t p, const char *ids, int unaligned, v2m_sin
 				}
 				copy_parallel(pieces, writer_threads);
 				if (row_done) for (u32 r(r0); r < r1; ++r) row_done(r, ctx);
+				continue;
+			}
+			if (row_sink)
+			{
+				// row bodies only, one call per row, in row order: the caller adds whatever surrounds a row
+				for (u32 r(r0); r < r1 && !st; ++r)
+					if (row_sink(r, h_buf[k] + u64(r - r0) * pitch, lengths[r], sink_ctx)) st = fail(V2M_ERR_STATE, "stream_rows: the sink reported an error");
 				continue;
 			}
 			for (u32 r(r0); r < r1 && !st; ++r)

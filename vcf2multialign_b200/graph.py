@@ -61,8 +61,9 @@ class DeviceGraph:
         """d_paths_by_edge_and_chrom_copy: optional DEVICE pointer to the edge-major path words (e.g. from synth.path_bits_device);
         the host arrays of `graph` are then not consulted for paths."""
         self.graph = graph
-        ref = np.frombuffer(bytes(ref_seq), dtype=np.uint8) if not isinstance(ref_seq, np.ndarray) else np.ascontiguousarray(ref_seq, dtype=np.uint8)
-        self.ref_len = int(ref.size)
+        # ref_seq None: the graph goes up without the reference (enough for find_cut_positions / find_matchings); attach_reference later
+        ref = None if ref_seq is None else (np.frombuffer(bytes(ref_seq), dtype=np.uint8) if not isinstance(ref_seq, np.ndarray) else np.ascontiguousarray(ref_seq, dtype=np.uint8))
+        self.ref_len = 0 if ref is None else int(ref.size)
         labels = np.frombuffer(graph.label_chars, dtype=np.uint8) if len(graph.label_chars) else np.zeros(1, np.uint8)
         v = _lib.GraphView()
         v.node_count, v.edge_count = graph.node_count(), graph.edge_count()
@@ -76,7 +77,7 @@ class DeviceGraph:
             v.paths_by_chrom_copy_and_edge = ptr(graph.paths_by_chrom_copy_and_edge)
         v.h_pad, v.e_pad = graph.h_pad, graph.e_pad
         v.total_chromosome_copies = graph.total_chromosome_copies()
-        v.ref_seq, v.ref_len = ptr(ref), ref.size
+        v.ref_seq, v.ref_len = ptr(ref), self.ref_len
         h = C.c_void_p()
         check(lib().v2m_cuda_graph_upload(C.byref(v), C.byref(h)))
         self._h = h
@@ -85,6 +86,11 @@ class DeviceGraph:
         if getattr(self, "_h", None):
             lib().v2m_cuda_graph_free(self._h)
             self._h = None
+
+    def attach_reference(self, ref_seq):
+        ref = np.frombuffer(bytes(ref_seq), dtype=np.uint8) if not isinstance(ref_seq, np.ndarray) else np.ascontiguousarray(ref_seq, dtype=np.uint8)
+        check(lib().v2m_cuda_graph_attach_reference(self._h, ptr(ref), ref.size))
+        self.ref_len = int(ref.size)
 
     __del__ = close
 

@@ -16,8 +16,11 @@
 #pragma once
 
 #include <cstdint>
+#include <concepts>
 #include <cstring>
+#include <exception>
 #include <limits>
+#include <memory>
 #include <ostream>
 #include <stdexcept>
 #include <string>
@@ -100,15 +103,8 @@ class device_graph
 {
 	v2m_graph_t m_handle{};
 
-public:
-	device_graph() = default;
-	device_graph(device_graph const &) = delete;
-	device_graph &operator=(device_graph const &) = delete;
-	device_graph(device_graph &&o) noexcept: m_handle(o.m_handle) { o.m_handle = nullptr; }
-	~device_graph() { if (m_handle) v2m_cuda_graph_free(m_handle); }
-
 	template <typename t_graph>
-	device_graph(sequence_type const &ref_seq, t_graph const &graph)
+	void upload(char const *ref_seq, std::uint64_t const ref_len, t_graph const &graph)
 	{
 		std::vector<std::uint64_t> label_offsets(graph.alt_edge_labels.size() + 1, 0);
 		std::string label_chars;
@@ -134,13 +130,75 @@ public:
 		// When the host graph has not been transposed yet (or was built without variant_graph.cc:453), K1 does it on the device.
 		view.paths_by_chrom_copy_and_edge = (ce.number_of_rows() == view.e_pad && ce.number_of_columns() == view.h_pad && !ce.values().empty()) ? ce.values().data() : nullptr;
 		view.total_chromosome_copies = graph.ploidy_csum.empty() ? 0 : graph.ploidy_csum.back();
-		view.ref_seq = ref_seq.data();
-		view.ref_len = ref_seq.size();
+		view.ref_seq = ref_seq;
+		view.ref_len = ref_len;
 		check(v2m_cuda_graph_upload(&view, &m_handle));
 	}
 
+public:
+	device_graph() = default;
+	device_graph(device_graph const &) = delete;
+	device_graph &operator=(device_graph const &) = delete;
+	device_graph(device_graph &&o) noexcept: m_handle(o.m_handle) { o.m_handle = nullptr; }
+	~device_graph() { if (m_handle) v2m_cuda_graph_free(m_handle); }
+
+	template <typename t_graph>
+	device_graph(sequence_type const &ref_seq, t_graph const &graph) { upload(ref_seq.data(), ref_seq.size(), graph); }
+
+	// Without the reference sequence: enough for find_cut_positions / find_matchings, which take none (output.hh:123, 126).
+	template <typename t_graph>
+	explicit device_graph(t_graph const &graph) { upload(nullptr, 0, graph); }
+
+	// Supplies the reference later (a no-op if the graph has it): rows can be written from then on.
+	void attach_reference(sequence_type const &ref_seq) const { check(v2m_cuda_graph_attach_reference(m_handle, ref_seq.data(), ref_seq.size())); }
+
 	v2m_graph_t get() const { return m_handle; }
 };
+
+namespace detail {
+
+	// The reference hands the same `variant_graph const &` to find_cut_positions, find_matchings and output_* one after the
+	// other (main.cc:489-549) and to output_sequence once per row (output.cc:34, 42). The graph is uploaded on the first of
+	// these calls and stays resident while the caller keeps passing the same, unchanged graph: identity is the address and
+	// size of its node, edge and path arrays (a graph edited in place between calls must be released by hand).
+	struct graph_key
+	{
+		void const *nodes{}, *targets{}, *paths{};
+		std::size_t n_nodes{}, n_edges{}, n_path_words{};
+		bool operator==(graph_key const &) const = default;
+	};
+
+	template <typename t_graph>
+	graph_key key_of(t_graph const &g)
+	{
+		return {g.reference_positions.data(), g.alt_edge_targets.data(), g.paths_by_edge_and_chrom_copy.values().data(),
+			g.reference_positions.size(), g.alt_edge_targets.size(), g.paths_by_edge_and_chrom_copy.values().size()};
+	}
+
+	class resident_graph
+	{
+		std::unique_ptr<device_graph>	m_graph;
+		graph_key						m_key;
+
+	public:
+		template <typename t_graph>
+		device_graph const &get(t_graph const &graph, sequence_type const *ref_seq)
+		{
+			graph_key const key(key_of(graph));
+			if (!m_graph || !(key == m_key))
+			{
+				m_graph.reset();
+				m_graph = ref_seq ? std::make_unique<device_graph>(*ref_seq, graph) : std::make_unique<device_graph>(graph);
+				m_key = key;
+			}
+			else if (ref_seq)
+				m_graph->attach_reference(*ref_seq);
+			return *m_graph;
+		}
+
+		void release() { m_graph.reset(); m_key = graph_key{}; }
+	};
+}
 
 class device_plan
 {
@@ -194,46 +252,74 @@ namespace detail {
 		return 0;
 	}
 
-	// One row of a plan as '>' id '\n' bytes (no trailing newline: sequence_writer.cc:35-36, 83-85).
-	inline void write_row(v2m_plan_t plan, std::uint32_t row, char const *fasta_identifier, bool unaligned, v2m_sink sink, void *sink_ctx)
+	// One row of a single-row plan as '>' id '\n' bytes (no trailing newline: sequence_writer.cc:35-36, 83-85), through the
+	// library's pinned block pipeline.
+	struct row_target { v2m_sink sink; void *sink_ctx; char const *fasta_identifier; };
+
+	inline int row_to_sink(std::uint32_t, const void *bytes, std::uint64_t n, void *ctx)
 	{
-		std::vector<std::uint64_t> lengths;
+		auto const &t(*static_cast<row_target const *>(ctx));
+		if (t.fasta_identifier)
 		{
-			std::uint32_t n_rows(0);
-			check(v2m_cuda_plan_row_count(plan, &n_rows));
-			lengths.resize(n_rows);
-			check(v2m_cuda_plan_row_lengths(plan, unaligned ? 1 : 0, lengths.data()));
+			std::string header(">");
+			header += t.fasta_identifier; header += '\n';
+			if (t.sink(header.data(), header.size(), t.sink_ctx)) return 1;
 		}
-		std::vector<std::uint8_t> bytes(lengths[row]);
-		if (!bytes.empty())
-		{
-			if (unaligned)
-			{
-				std::uint64_t const off(0);
-				check(v2m_cuda_emit_rows_unaligned(plan, row, row + 1, &off, bytes.data()));
-			}
-			else
-				check(v2m_cuda_emit_rows(plan, row, row + 1, 0, lengths[row], bytes.data(), lengths[row]));
-		}
-		std::string header;
-		if (fasta_identifier) { header += '>'; header += fasta_identifier; header += '\n'; }
-		if ((!header.empty() && sink(header.data(), header.size(), sink_ctx)) || (!bytes.empty() && sink(bytes.data(), bytes.size(), sink_ctx)))
-			throw error("output_sequence: write failed");
+		return n ? t.sink(bytes, n, t.sink_ctx) : 0;
 	}
+
+	inline void write_row(v2m_plan_t plan, char const *fasta_identifier, bool unaligned, v2m_sink sink, void *sink_ctx)
+	{
+		row_target target{sink, sink_ctx, fasta_identifier};
+		check(v2m_cuda_stream_rows(plan, unaligned ? 1 : 0, &row_to_sink, &target));
+	}
+
+	inline resident_graph &thread_resident_graph() { thread_local resident_graph rg; return rg; }
 }
 
+// Frees the graph the free functions below keep resident for the calling thread.
+inline void release_resident_graph() { detail::thread_resident_graph().release(); }
+
 // v2m::output_sequence(ref_seq, graph, stream, fasta_identifier, should_output_unaligned, delegate) — sequence_writer.cc:22-85.
-// Uploads the graph for one row; the output classes below keep the graph resident across rows instead.
+// The reference calls this once per row (output.cc:34, 42): the graph is uploaded by the first call and stays resident for
+// the calling thread while the same graph is passed (detail::resident_graph; release_resident_graph() drops it).
 template <typename t_graph>
 void output_sequence(sequence_type const &ref_seq, t_graph const &graph, std::ostream &stream, char const *fasta_identifier,
 	bool const should_output_unaligned, sequence_writing_delegate &delegate)
 {
-	device_graph const dg(ref_seq, graph);
+	device_graph const &dg(detail::thread_resident_graph().get(graph, &ref_seq));
 	v2m_plan_t p{};
 	std::uint32_t const idx(delegate.chromosome_copy_index);
 	check(v2m_cuda_plan_haplotypes(dg.get(), &idx, 1, &p));
 	device_plan const plan(p);
-	detail::write_row(plan.get(), 0, fasta_identifier, should_output_unaligned, detail::ostream_sink, &stream);
+	detail::write_row(plan.get(), fasta_identifier, should_output_unaligned, detail::ostream_sink, &stream);
+}
+
+// The lb::file_handle & overload (sequence_writer.hh:48-56, sequence_writer.cc:88-100) — the one output::output_sequence_file
+// calls (output.cc:34, 42). Anything with get() returning the descriptor will do; the bytes go out with write(2) and the
+// descriptor stays open, as with the reference's never-closing lb::file_ostream.
+struct file_handle					// stand-in for lb::file_handle (lib/libbio/include/libbio/file_handle.hh): owns the descriptor
+{
+	int fd{-1};
+	explicit file_handle(int const fd_): fd(fd_) {}
+	file_handle(file_handle const &) = delete;
+	file_handle &operator=(file_handle const &) = delete;
+	~file_handle() { if (fd >= 0) ::close(fd); }
+	int get() const { return fd; }
+};
+
+template <typename t_graph, typename t_handle>
+requires requires(t_handle &h) { { h.get() } -> std::convertible_to<int>; }
+void output_sequence(sequence_type const &ref_seq, t_graph const &graph, t_handle &handle, char const *fasta_identifier,
+	bool const should_output_unaligned, sequence_writing_delegate &delegate)
+{
+	device_graph const &dg(detail::thread_resident_graph().get(graph, &ref_seq));
+	v2m_plan_t p{};
+	std::uint32_t const idx(delegate.chromosome_copy_index);
+	check(v2m_cuda_plan_haplotypes(dg.get(), &idx, 1, &p));
+	device_plan const plan(p);
+	int fd(handle.get());
+	detail::write_row(plan.get(), fasta_identifier, should_output_unaligned, detail::fd_sink, &fd);
 }
 
 
@@ -261,6 +347,7 @@ protected:
 	output_delegate	*m_delegate{};
 	bool			m_should_output_reference{};
 	bool			m_should_output_unaligned{};
+	detail::resident_graph	m_resident;			// the graph on the device, kept across find_* / output_* calls on the same graph
 
 	struct row_desc { std::string a2m_id; std::string file_stem; };
 
@@ -344,35 +431,56 @@ public:
 		pid_t child;
 		int fd(open_destination(dst_name, child));
 		if (fd < 0) return;
-		try { stream_a2m(ref_seq, graph, detail::fd_sink, &fd); }
+		// A regular file (opened read-write above) is filled through a shared mapping by several threads inside the library;
+		// the stdin of a --pipe subprocess takes sequential write(2).
+		try { stream_a2m(ref_seq, graph, detail::fd_sink, &fd, child > 0 ? -1 : fd); }
 		catch (...) { ::close(fd); if (child > 0) ::waitpid(child, nullptr, 0); throw; }
 		::close(fd);
 		if (child > 0) m_delegate->exit_subprocess(child);
 	}
 
 	// One file (or --pipe subprocess) per row; the file name doubles as the FASTA identifier and there is no trailing
-	// newline (output.cc:18-44).
+	// newline (output.cc:18-44). The rows come block-wise out of the same pinned two-stream pipeline as the A2M stream
+	// (v2m_cuda_stream_rows); each row's file is opened, written and closed from the calling thread, in row order.
 	void output_separate(sequence_type const &ref_seq, t_graph const &graph, bool const should_include_fasta_header)
 	{
-		device_graph const dg(ref_seq, graph);
+		device_graph const &dg(m_resident.get(graph, &ref_seq));
 		std::vector<row_desc> rows;
 		device_plan const plan(make_plan(dg, graph, rows));
-		for (std::uint32_t r(0); r < rows.size(); ++r)
-		{
-			before_row(graph, r);
-			std::string const name(file_name(rows[r].file_stem, should_include_fasta_header));
-			pid_t child;
-			int fd(open_destination(name.c_str(), child));
-			if (fd < 0) continue;
-			try { detail::write_row(plan.get(), r, name.c_str(), m_should_output_unaligned, detail::fd_sink, &fd); }
-			catch (...) { ::close(fd); if (child > 0) ::waitpid(child, nullptr, 0); throw; }
-			::close(fd);
-			if (child > 0) m_delegate->exit_subprocess(child);
-			after_row(r, false);
-		}
+		separate_ctx ctx{this, &graph, &rows, should_include_fasta_header, nullptr};
+		int const status(v2m_cuda_stream_rows(plan.get(), m_should_output_unaligned ? 1 : 0, &separate_row, &ctx));
+		if (ctx.failure) std::rethrow_exception(ctx.failure);
+		check(status);
 	}
 
+	// Drops the device copy of the graph (it is also dropped with the object).
+	void release_device_graph() { m_resident.release(); }
+
 private:
+	struct separate_ctx { output_t *self; t_graph const *graph; std::vector<row_desc> const *rows; bool fasta_header; std::exception_ptr failure; };
+
+	static int separate_row(std::uint32_t const r, const void *bytes, std::uint64_t const n, void *ctx_)
+	{
+		auto &ctx(*static_cast<separate_ctx *>(ctx_));
+		output_t &self(*ctx.self);
+		try
+		{
+			self.before_row(*ctx.graph, r);
+			std::string const name(self.file_name((*ctx.rows)[r].file_stem, ctx.fasta_header));
+			pid_t child;
+			int fd(self.open_destination(name.c_str(), child));
+			if (fd < 0) return 0;										// the delegate has been told (unable_to_execute_subprocess)
+			std::string const header('>' + name + '\n');				// output.cc:36, 42: the file name is the FASTA identifier
+			bool const ok(0 == detail::fd_sink(header.data(), header.size(), &fd) && (0 == n || 0 == detail::fd_sink(bytes, n, &fd)));
+			::close(fd);
+			if (!ok) { if (child > 0) ::waitpid(child, nullptr, 0); throw error("output_separate: write to " + name + " failed"); }
+			if (child > 0) self.m_delegate->exit_subprocess(child);
+			self.after_row(r, false);
+			return 0;
+		}
+		catch (...) { ctx.failure = std::current_exception(); return 1; }
+	}
+
 	struct hook_ctx { output_t *self; t_graph const *graph; std::uint32_t next_before{}; std::uint32_t n_rows{}; };
 
 	static void row_done(std::uint32_t row, void *ctx)
@@ -382,15 +490,16 @@ private:
 		h.self->after_row(row, true);
 	}
 
-	void stream_a2m(sequence_type const &ref_seq, t_graph const &graph, v2m_sink sink, void *sink_ctx)
+	void stream_a2m(sequence_type const &ref_seq, t_graph const &graph, v2m_sink sink, void *sink_ctx, int const file_fd = -1)
 	{
-		device_graph const dg(ref_seq, graph);
+		device_graph const &dg(m_resident.get(graph, &ref_seq));
 		std::vector<row_desc> rows;
 		device_plan const plan(make_plan(dg, graph, rows));
 		std::string ids;
 		for (auto const &r : rows) { ids += r.a2m_id; ids += '\0'; }
 		hook_ctx ctx{this, &graph, 0, std::uint32_t(rows.size())};
-		check(v2m_cuda_stream_a2m(plan.get(), ids.data(), m_should_output_unaligned ? 1 : 0, sink, sink_ctx, &row_done, &ctx));
+		if (file_fd >= 0) check(v2m_cuda_write_a2m(plan.get(), ids.data(), m_should_output_unaligned ? 1 : 0, file_fd, &row_done, &ctx));
+		else check(v2m_cuda_stream_a2m(plan.get(), ids.data(), m_should_output_unaligned ? 1 : 0, sink, sink_ctx, &row_done, &ctx));
 	}
 };
 
@@ -528,11 +637,22 @@ public:
 	}
 	[[nodiscard]] std::uint64_t minimum_distance() const { return m_min_distance; }
 
+	// founder_sequence_greedy_output::load_cut_positions / output_cut_positions (output.hh:121-122, founder_…cc:121-136): the
+	// reference's cereal PortableBinary file, byte for byte. Defined in host/v2m_cereal.hh (include it to use them).
+	void load_cut_positions(char const *path);
+	void output_cut_positions(char const *path) const;
+
 	// output.hh:123, founder_sequence_greedy_output.cc:139-152 → find_initial_cut_positions_lambda_min (find_cut_positions.cc:93-211).
+	// The reference's parameter list: the sweep needs no reference sequence, so the graph goes up without one and stays
+	// resident for find_matchings (which then starts from the pBWT states this call leaves behind) and for output_*.
+	[[nodiscard]] bool find_cut_positions(t_graph const &graph, std::uint64_t const minimum_distance)
+	{
+		return find_cut_positions(this->m_resident.get(graph, nullptr), graph, minimum_distance);
+	}
+
 	[[nodiscard]] bool find_cut_positions(sequence_type const &ref_seq, t_graph const &graph, std::uint64_t const minimum_distance)
 	{
-		device_graph const dg(ref_seq, graph);
-		return find_cut_positions(dg, graph, minimum_distance);
+		return find_cut_positions(this->m_resident.get(graph, &ref_seq), graph, minimum_distance);
 	}
 
 	[[nodiscard]] bool find_cut_positions(device_graph const &dg, t_graph const &graph, std::uint64_t const minimum_distance)
@@ -550,10 +670,15 @@ public:
 		return true;
 	}
 
+	// output.hh:126, founder_sequence_greedy_output.cc:154-512.
+	[[nodiscard]] bool find_matchings(t_graph const &graph, ploidy_type const founder_count)
+	{
+		return find_matchings(this->m_resident.get(graph, nullptr), founder_count);
+	}
+
 	[[nodiscard]] bool find_matchings(sequence_type const &ref_seq, t_graph const &graph, ploidy_type const founder_count)
 	{
-		device_graph const dg(ref_seq, graph);
-		return find_matchings(dg, founder_count);
+		return find_matchings(this->m_resident.get(graph, &ref_seq), founder_count);
 	}
 
 	[[nodiscard]] bool find_matchings(device_graph const &dg, ploidy_type const founder_count)						// :154-512

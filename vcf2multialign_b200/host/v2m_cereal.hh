@@ -226,4 +226,11 @@ void output_cut_positions(founder_sequence_greedy_output_t<t_graph> const &out, 
 	save_cut_positions(os, cut_positions_file{out.cut_positions(), out.minimum_distance(), out.max_segmentation_height()});
 }
 
+// The members with the reference's names (output.hh:121-122), declared in v2m_b200.hh.
+template <typename t_graph>
+void founder_sequence_greedy_output_t<t_graph>::load_cut_positions(char const *path) { v2m_b200::load_cut_positions(*this, path); }
+
+template <typename t_graph>
+void founder_sequence_greedy_output_t<t_graph>::output_cut_positions(char const *path) const { v2m_b200::output_cut_positions(*this, path); }
+
 } // namespace v2m_b200
