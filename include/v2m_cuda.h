@@ -247,6 +247,16 @@ int v2m_cuda_paths_from_genotypes_device(const uint16_t *gt, uint64_t n_records,
                                          uint64_t h_pad, uint64_t e_pad, void *d_paths,
                                          uint64_t *overlaps, uint64_t overlap_cap, uint64_t *n_overlaps);
 
+/* Both orientations born on the device: d_paths_by_edge_and_chrom_copy as above and d_paths_by_chrom_copy_and_edge (the matrix
+ * build_variant_graph derives at its end with transpose_matrix, variant_graph.cc:447-453), filled a range of final edge columns
+ * at a time after every record block, while the block's columns are still in the L2 — a graph built this way (both pointers in
+ * v2m_graph_view with paths_on_device = 1) never runs K1 over the whole matrix. */
+int v2m_cuda_paths_from_genotypes_both(const uint16_t *gt, uint64_t n_records, uint32_t n_copies,
+                                       const uint64_t *alt_offsets, const uint64_t *edges_by_alt,
+                                       const uint64_t *record_ref_pos, const uint64_t *edge_target_pos, uint64_t n_edges,
+                                       uint64_t h_pad, uint64_t e_pad, void *d_paths_by_edge_and_chrom_copy, void *d_paths_by_chrom_copy_and_edge,
+                                       uint64_t *overlaps, uint64_t overlap_cap, uint64_t *n_overlaps);
+
 /* --- synthetic workloads (measurement infrastructure) ------------------------------------------------ */
 /* Fills d_dst (device, e_pad × h_pad/64 words = paths_by_edge_and_chrom_copy) with LD-structured path bits that are a
  * pure function of (seed, chromosome copy, site); per edge: its site, its 0-based ALT number, the site's ALT count. */

@@ -694,6 +694,28 @@ def test_ingest_genotypes_random_graphs(v2m, tmp_path):
     assert overlaps > 0
 
 
+@pytest.mark.parametrize("block_records", [None, "7", "64"])
+def test_ingest_genotypes_both_orientations(v2m, tmp_path, expected, golden_dir, monkeypatch, block_records):
+    """K5 with paths_by_chrom_copy_and_edge born next to paths_by_edge_and_chrom_copy (variant_graph.cc:379-425 + :453): both equal
+    the oracle builder's matrices, with the record blocks forced small so that ranges of final edge columns are transposed
+    block by block, word-straddling edges included."""
+    if block_records:
+        monkeypatch.setenv("V2M_K5_BLOCK_RECORDS", block_records)
+    import glob
+    graphs = []
+    for vcf in sorted(glob.glob(os.path.join(golden_dir, "*", "*.vcf"))):
+        fa = vcf[:-4] + ".fa"
+        graphs.append(orc.Graph.from_files(fa if os.path.exists(fa) else os.path.join(os.path.dirname(vcf), "test-1.fa"), vcf, "1"))
+    graphs += [rg.random_oracle_graph(str(tmp_path), 700 + i, ref_len=3000 + 500 * i, n_records=300 + 150 * i, n_samples=20 + 30 * i, ploidy=2, many_alts_prob=0.1)
+               for i in range(3)]
+    for k, og in enumerate(graphs):
+        t = og.genotype_trace()
+        a = og.arrays()
+        ec, ce = v2m.paths_from_genotypes_both(t["gt"], t["alt_offsets"], t["edges_by_alt"], a["h_pad"], a["e_pad"])
+        assert np.array_equal(ec, a["paths_ec"]), k
+        assert np.array_equal(ce, a["paths_ce"]), k
+
+
 def test_ingest_genotypes_rejects_bad_allele(v2m):
     gt = np.array([[0, 2, 0, 0]], np.uint16)            # ALT 2 of a record with one ALT
     with pytest.raises(v2m.V2MError):

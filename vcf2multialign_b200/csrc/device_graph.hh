@@ -79,6 +79,7 @@ struct device_plan
 };
 
 int launch_transpose_bits(void const *d_src, u64 rows, u64 cols, void *d_dst, cudaStream_t stream);
+int launch_transpose_bits_into(void const *d_src, u64 rows, u64 cols, void *d_dst, u64 dst_line_bits, cudaStream_t stream);
 int launch_build_template(device_graph const &g, cudaStream_t stream);
 int launch_check_assigned(u32 const *d_assigned, u64 n, u32 H, u32 *d_bad, cudaStream_t stream);
 int launch_compose_founders(device_graph const &g, u64 const *d_cut_edges, u64 n_segments, u32 const *d_assigned, u32 n_founders, u64 *d_out, cudaStream_t stream);

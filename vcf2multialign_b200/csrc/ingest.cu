@@ -25,6 +25,7 @@
 
 #include "../../include/v2m_cuda.h"
 #include "common.cuh"
+#include "device_graph.hh"
 
 namespace v2m {
 
@@ -259,9 +260,16 @@ namespace {
 }
 
 // Core: fills d_paths (device, e_pad × h_pad / 64 words, zeroed here). gt is host memory and is streamed in record blocks.
+// d_paths_he (optional): paths_by_chrom_copy_and_edge, the orientation build_variant_graph derives with transpose_matrix at its
+// end (variant_graph.cc:453). Here it is born with the bits: after every record block the edge columns that are final — all
+// edges below the smallest edge index of any later record, in whole 64-edge words — are transposed into their place in the
+// copy-major lines while the block's output is still in the L2 (a block writes ~4 MB of edge columns), so a graph built on
+// the device never runs K1 over the whole matrix. Fusing the transposed stores into the ingest kernel itself was considered
+// and not done: a warp holds one record's 1 – 2 edge columns, the copy-major lines want 32 consecutive edges per word, and
+// K5 is bound by reading 2 bytes per genotype — the transposed orientation is 6 % of its traffic.
 int paths_from_genotypes_device(unsigned short const *gt, u64 const n_records, u32 const H, u64 const *alt_offsets, u64 const *edges_by_alt,
 	u64 const *record_ref_pos, u64 const *edge_target_pos, u64 const n_edges, u64 const h_pad, u64 const e_pad, void *d_paths,
-	std::vector<u64> *overlaps)
+	std::vector<u64> *overlaps, void *d_paths_he = nullptr)
 {
 	if (0 != h_pad % 64 || 0 != e_pad % 64 || h_pad < H) return fail(V2M_ERR_ARGUMENT, "paths_from_genotypes: path matrix dimensions must be multiples of 64 covering all chromosome copies");
 	if (n_records && (!gt || !alt_offsets)) return fail(V2M_ERR_ARGUMENT, "paths_from_genotypes: NULL argument");
@@ -270,10 +278,30 @@ int paths_from_genotypes_device(unsigned short const *gt, u64 const n_records, u
 	bool const want_overlaps(overlaps && record_ref_pos && edge_target_pos);
 	if (overlaps) overlaps->clear();
 	V2M_CUDA_TRY(cudaMemset(d_paths, 0, e_pad * h_pad / 8));
-	if (0 == n_records || 0 == H) return V2M_OK;
+	if (0 == n_records || 0 == H)
+	{
+		if (d_paths_he) V2M_CUDA_TRY(cudaMemset(d_paths_he, 0, e_pad * h_pad / 8));
+		return V2M_OK;
+	}
 
 	u32 const Wh32(u32(h_pad / 32));
-	u64 const block_records(std::max<u64>(1, std::min<u64>(n_records, (u64(64) << 20) / (u64(H) * 2))));		// ~64 MB of GT values per block
+	u64 block_records(std::max<u64>(1, std::min<u64>(n_records, (u64(64) << 20) / (u64(H) * 2))));		// ~64 MB of GT values per block
+	if (char const *env = std::getenv("V2M_K5_BLOCK_RECORDS"))		// tests force small blocks
+		if (long long const v = std::atoll(env); v > 0) block_records = std::min<u64>(n_records, u64(v));
+	// Smallest edge index of any ALT of record r or later: the edge columns below it are final once records < r are done.
+	std::vector<u64> frontier;
+	if (d_paths_he)
+	{
+		frontier.assign(n_records + 1, e_pad);
+		for (u64 r(n_records); r-- > 0; )
+		{
+			u64 m(frontier[r + 1]);
+			for (u64 a(alt_offsets[r]); a < alt_offsets[r + 1]; ++a)
+				if (EDGE_NONE != edges_by_alt[a]) m = std::min(m, edges_by_alt[a]);
+			frontier[r] = m;
+		}
+	}
+	u64 transposed_upto(0);			// edge columns [0, transposed_upto) are in d_paths_he already (a multiple of 64)
 
 	dbuf d_gt[2], d_off, d_eba, d_ref, d_tgt, d_state, d_pairs, d_count, d_bad;
 	if (d_gt[0].alloc(block_records * H * 2) || d_gt[1].alloc(block_records * H * 2) || d_off.alloc((n_records + 1) * 8) || d_eba.alloc(n_alts * 8) || d_bad.alloc(4))
@@ -360,11 +388,31 @@ int paths_from_genotypes_device(unsigned short const *gt, u64 const n_records, u
 					d_ref.as<u64>() + r0, d_tgt.as<u64>(), n_edges, d_state.as<u64>(), d_pairs.as<u64>(), pair_cap, d_count.as<unsigned long long>());
 				V2M_CHECK_LAUNCH("genotype_overlaps_kernel");
 			}
+			if (0 == attempt && d_paths_he)
+			{
+				u64 const upto(std::min(frontier[r0 + nr], e_pad) / 64 * 64);
+				if (upto > transposed_upto)
+				{
+					// the range may reach back into columns the previous block (other stream) wrote
+					if (!first && !want_overlaps) V2M_CUDA_TRY(cudaStreamWaitEvent(st, done[k ^ 1], 0));
+					if (int const rc = launch_transpose_bits_into(static_cast<u64 const *>(d_paths) + transposed_upto * (h_pad / 64), h_pad, upto - transposed_upto,
+							static_cast<u64 *>(d_paths_he) + transposed_upto / 64, e_pad, st)) return rc;
+					transposed_upto = upto;
+				}
+			}
 			V2M_CUDA_TRY(cudaEventRecord(done[k], st));
 			first = false;
 		}
 		V2M_CUDA_TRY(cudaStreamSynchronize(streams[0]));
 		V2M_CUDA_TRY(cudaStreamSynchronize(streams[1]));
+		if (0 == attempt && d_paths_he && transposed_upto < e_pad)
+		{
+			// what is left: the last partial word's columns and the zero padding up to e_pad
+			if (int const rc = launch_transpose_bits_into(static_cast<u64 const *>(d_paths) + transposed_upto * (h_pad / 64), h_pad, e_pad - transposed_upto,
+					static_cast<u64 *>(d_paths_he) + transposed_upto / 64, e_pad, nullptr)) return rc;
+			transposed_upto = e_pad;
+			V2M_CUDA_TRY(cudaDeviceSynchronize());
+		}
 		u32 bad(0);
 		V2M_CUDA_TRY(cudaMemcpy(&bad, d_bad.p, 4, cudaMemcpyDeviceToHost));
 		if (bad & 1u) return fail(V2M_ERR_ARGUMENT, "paths_from_genotypes: a genotype refers to an ALT its record does not have (the reference asserts, variant_graph.cc:399)");
@@ -404,6 +452,27 @@ extern "C" int v2m_cuda_paths_from_genotypes_device(const uint16_t *gt, uint64_t
 	bool const want(nullptr != n_overlaps);
 	if (int const st = paths_from_genotypes_device(gt, n_records, n_copies, alt_offsets, edges_by_alt, record_ref_pos, edge_target_pos, n_edges,
 			h_pad, e_pad, d_paths, want ? &ov : nullptr)) return st;
+	if (want)
+	{
+		*n_overlaps = ov.size() / 2;
+		if (ov.size() / 2 > overlap_cap || (!overlaps && !ov.empty()))
+			return fail(V2M_ERR_ARGUMENT, "paths_from_genotypes: overlap capacity too small (needed count is in *n_overlaps)");
+		std::copy(ov.begin(), ov.end(), overlaps);
+	}
+	return V2M_OK;
+}
+
+extern "C" int v2m_cuda_paths_from_genotypes_both(const uint16_t *gt, uint64_t n_records, uint32_t n_copies,
+	const uint64_t *alt_offsets, const uint64_t *edges_by_alt, const uint64_t *record_ref_pos, const uint64_t *edge_target_pos, uint64_t n_edges,
+	uint64_t h_pad, uint64_t e_pad, void *d_paths_by_edge_and_chrom_copy, void *d_paths_by_chrom_copy_and_edge,
+	uint64_t *overlaps, uint64_t overlap_cap, uint64_t *n_overlaps)
+{
+	using namespace v2m;
+	if (!d_paths_by_edge_and_chrom_copy || !d_paths_by_chrom_copy_and_edge) return fail(V2M_ERR_ARGUMENT, "paths_from_genotypes_both: NULL output");
+	std::vector<u64> ov;
+	bool const want(nullptr != n_overlaps);
+	if (int const st = paths_from_genotypes_device(gt, n_records, n_copies, alt_offsets, edges_by_alt, record_ref_pos, edge_target_pos, n_edges,
+			h_pad, e_pad, d_paths_by_edge_and_chrom_copy, want ? &ov : nullptr, d_paths_by_chrom_copy_and_edge)) return st;
 	if (want)
 	{
 		*n_overlaps = ov.size() / 2;

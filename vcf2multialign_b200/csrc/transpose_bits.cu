@@ -83,9 +83,10 @@ constexpr int K1_TW = 32;			// 32-bit words per line per tile (1024 bits)
 constexpr int K1_THREADS = 512;
 
 __global__ void __launch_bounds__(K1_THREADS, 2)
-transpose_bits_kernel(u64 const * __restrict__ src, u32 * __restrict__ dst, u64 const R64, u64 const C)
+transpose_bits_kernel(u64 const * __restrict__ src, u32 * __restrict__ dst, u64 const R64, u64 const C, u64 const dst_pitch32)
 {
-	// R64 = source rows / 64 = 64-bit words per source line; C = number of source lines.
+	// R64 = source rows / 64 = 64-bit words per source line; C = number of source lines; dst_pitch32 = 32-bit words between
+	// destination lines (C / 32 for a whole matrix, more when the lines being written are a column range of longer ones).
 	extern __shared__ __align__(16) u64 tile[];					// K1_TC * K1_TW / 2 words = 64 KiB (dynamic: above the 48 KiB static limit)
 
 	// Row bands vary fastest (blockIdx.x): the CTAs that share the boundary sectors of a 128-byte piece of a source line run
@@ -137,10 +138,10 @@ transpose_bits_kernel(u64 const * __restrict__ src, u32 * __restrict__ dst, u64 
 	u64 const r0(64 * p0 + 32 * yw);							// first destination line of this sub-tile
 	if (xw < C32 && r0 < 64 * R64)								// rows are a multiple of 64, sub-tiles of 32: all-or-nothing
 	{
-		u32 *out(dst + r0 * C32 + xw);
+		u32 *out(dst + r0 * dst_pitch32 + xw);
 #pragma unroll
 		for (int j = 0; j < 32; ++j)
-			k1_store(out + u64(j) * C32, a[j], st_policy);
+			k1_store(out + u64(j) * dst_pitch32, a[j], st_policy);
 	}
 }
 
@@ -155,7 +156,7 @@ constexpr int K1T_TC = 1024;
 constexpr int K1T_TW = 16;
 
 __global__ void __launch_bounds__(K1_THREADS, 2)
-transpose_bits_tall_kernel(u64 const * __restrict__ src, u32 * __restrict__ dst, u64 const R64, u64 const C)
+transpose_bits_tall_kernel(u64 const * __restrict__ src, u32 * __restrict__ dst, u64 const R64, u64 const C, u64 const dst_pitch32)
 {
 	extern __shared__ __align__(16) u64 tile[];					// K1T_TC · K1T_TW words + 16 words of padding
 	u64 const c0(u64(blockIdx.y) * K1T_TC);
@@ -201,10 +202,10 @@ transpose_bits_tall_kernel(u64 const * __restrict__ src, u32 * __restrict__ dst,
 	u64 const r0(64 * p0 + 32 * yw);
 	if (xw < C32 && r0 < 64 * R64)
 	{
-		u32 *out(dst + r0 * C32 + xw);
+		u32 *out(dst + r0 * dst_pitch32 + xw);
 #pragma unroll
 		for (int j = 0; j < 32; ++j)
-			k1_store(out + u64(j) * C32, a[j], st_policy);
+			k1_store(out + u64(j) * dst_pitch32, a[j], st_policy);
 	}
 }
 
@@ -371,10 +372,14 @@ transpose_bits_sheared_kernel(u64 const * __restrict__ src, u8 * __restrict__ ds
 }
 
 
-int launch_transpose_bits(void const *d_src, u64 rows, u64 cols, void *d_dst, cudaStream_t stream)
+
+// dst_line_bits >= cols: the destination lines written are the first cols bits of lines that are dst_line_bits long (K5 fills
+// paths_by_chrom_copy_and_edge a range of edge columns at a time; d_dst then points at the range's first word of line 0).
+int launch_transpose_bits_into(void const *d_src, u64 rows, u64 cols, void *d_dst, u64 dst_line_bits, cudaStream_t stream)
 {
 	if (0 == cols || 0 == rows) return 0;
 	u64 const R64(rows / 64);
+	u64 const dst_pitch32(dst_line_bits / 32);
 	int const force([] { char const *env(std::getenv("V2M_K1_TALL")); return env ? std::atoi(env) : -1; }());	// experiments and tests: 0 / 1 / 2 (2: the sheared kernel wherever its grid allows)
 	{
 		// The path matrix as build_variant_graph hands it over (rows = chromosome copies, one source line per edge) and anything
@@ -386,7 +391,7 @@ int launch_transpose_bits(void const *d_src, u64 rows, u64 cols, void *d_dst, cu
 		bool const any_shift(0 != (sh.rows[1] | sh.rows[2] | sh.rows[3]));
 		u64 const n_tiles((LB + (any_shift ? 24 : 0) + 127) / 128);
 		bool const fits(n_tiles <= 65535u && n_bands <= 0x7fffffffu);
-		if (fits && 2 == force)		// opt-in: measured slower than the tile kernels on every shape (see the kernel's header)
+		if (fits && 2 == force && dst_line_bits == cols)		// opt-in: measured slower than the tile kernels on every shape (see the kernel's header)
 		{
 			V2M_CUDA_TRY(cudaFuncSetAttribute(transpose_bits_sheared_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, K1H_SMEM));
 			transpose_bits_sheared_kernel<<<dim3(unsigned(n_bands), unsigned(n_tiles)), K1_THREADS, K1H_SMEM, stream>>>(
@@ -402,7 +407,7 @@ int launch_transpose_bits(void const *d_src, u64 rows, u64 cols, void *d_dst, cu
 		if (grid.y > 65535u) return fail(1, "transpose_bits: too many source lines in one launch");
 		constexpr int smem_bytes((K1T_TC * K1T_TW + 16) * sizeof(u32));
 		V2M_CUDA_TRY(cudaFuncSetAttribute(transpose_bits_tall_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
-		transpose_bits_tall_kernel<<<grid, K1_THREADS, smem_bytes, stream>>>(static_cast<u64 const *>(d_src), static_cast<u32 *>(d_dst), R64, cols);
+		transpose_bits_tall_kernel<<<grid, K1_THREADS, smem_bytes, stream>>>(static_cast<u64 const *>(d_src), static_cast<u32 *>(d_dst), R64, cols, dst_pitch32);
 		V2M_CHECK_LAUNCH("transpose_bits_tall_kernel");
 		return 0;
 	}
@@ -410,9 +415,14 @@ int launch_transpose_bits(void const *d_src, u64 rows, u64 cols, void *d_dst, cu
 	if (grid.y > 65535u) return fail(1, "transpose_bits: more than 33,553,920 source lines in one launch");
 	constexpr int smem_bytes(K1_TC * (K1_TW / 2) * sizeof(u64));
 	V2M_CUDA_TRY(cudaFuncSetAttribute(transpose_bits_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));	// per device
-	transpose_bits_kernel<<<grid, K1_THREADS, smem_bytes, stream>>>(static_cast<u64 const *>(d_src), static_cast<u32 *>(d_dst), R64, cols);
+	transpose_bits_kernel<<<grid, K1_THREADS, smem_bytes, stream>>>(static_cast<u64 const *>(d_src), static_cast<u32 *>(d_dst), R64, cols, dst_pitch32);
 	V2M_CHECK_LAUNCH("transpose_bits_kernel");
 	return 0;
+}
+
+int launch_transpose_bits(void const *d_src, u64 rows, u64 cols, void *d_dst, cudaStream_t stream)
+{
+	return launch_transpose_bits_into(d_src, rows, cols, d_dst, cols, stream);
 }
 
 } // namespace v2m

@@ -275,3 +275,27 @@ def paths_from_genotypes(gt, alt_offsets, edges_by_alt, h_pad: int, e_pad: int, 
         check(st)
         break
     return out[: h_pad * e_pad // 64], (ov[: 2 * n.value].reshape(-1, 2) if want else None)
+
+
+def paths_from_genotypes_both(gt, alt_offsets, edges_by_alt, h_pad: int, e_pad: int):
+    """K5 with both orientations born on the device (v2m_cuda_paths_from_genotypes_both): returns the words of
+    paths_by_edge_and_chrom_copy and of paths_by_chrom_copy_and_edge."""
+    gt = np.ascontiguousarray(gt, dtype=np.uint16)
+    R, Hc = (gt.shape if gt.ndim == 2 else (0, 0))
+    off = np.ascontiguousarray(alt_offsets, dtype=np.uint64)
+    eba = np.ascontiguousarray(edges_by_alt, dtype=np.uint64)
+    n_bytes = max(h_pad * e_pad // 8, 16)
+    L = lib()
+    d_ec, d_ce = L.v2m_cuda_device_alloc(n_bytes), L.v2m_cuda_device_alloc(n_bytes)
+    if not d_ec or not d_ce:
+        raise V2MError("device_alloc failed")
+    try:
+        check(L.v2m_cuda_paths_from_genotypes_both(ptr(gt), R, Hc, ptr(off), ptr(eba) if eba.size else None, None, None, 0, h_pad, e_pad, d_ec, d_ce, None, 0, None))
+        ec, ce = np.zeros(max(h_pad * e_pad // 64, 1), np.uint64), np.zeros(max(h_pad * e_pad // 64, 1), np.uint64)
+        if h_pad * e_pad:
+            check(L.v2m_cuda_memcpy_d2h(ptr(ec), d_ec, h_pad * e_pad // 8))
+            check(L.v2m_cuda_memcpy_d2h(ptr(ce), d_ce, h_pad * e_pad // 8))
+    finally:
+        L.v2m_cuda_device_free(d_ec)
+        L.v2m_cuda_device_free(d_ce)
+    return ec[: h_pad * e_pad // 64], ce[: h_pad * e_pad // 64]
