@@ -87,6 +87,33 @@ def main():
     dt = times[1]
     out["e2e"] = {"seconds": dt, "first_call_seconds": times[0], "genotypes_per_s": R * H / dt, "h2d_bytes": int(gt.nbytes), "overlaps": int(len(ov))}
 
+    # both orientations born on the device (v2m_cuda_paths_from_genotypes_both) against the edge-major one alone, host GT block in,
+    # matrices left on the device; the copy-major result must be the transpose of the edge-major one
+    d_ec, d_ce = L.v2m_cuda_device_alloc(h_pad * e_pad // 8), L.v2m_cuda_device_alloc(h_pad * e_pad // 8)
+    t_one, t_both = [], []
+    for _ in range(3):
+        t0 = time.perf_counter()
+        check(L.v2m_cuda_paths_from_genotypes_device(ptr(gt), R, H, ptr(alt_offsets), ptr(edges_by_alt), None, None, 0, h_pad, e_pad, d_ec, None, 0, None))
+        t_one.append(time.perf_counter() - t0)
+        t0 = time.perf_counter()
+        check(L.v2m_cuda_paths_from_genotypes_both(ptr(gt), R, H, ptr(alt_offsets), ptr(edges_by_alt), None, None, 0, h_pad, e_pad, d_ec, d_ce, None, 0, None))
+        t_both.append(time.perf_counter() - t0)
+    ce = np.zeros(h_pad * e_pad // 64, np.uint64)
+    check(L.v2m_cuda_memcpy_d2h(ptr(ce), d_ce, ce.nbytes))
+    d_t = L.v2m_cuda_device_alloc(h_pad * e_pad // 8)
+    check(L.v2m_cuda_transpose_bits_device(d_ec, h_pad, e_pad, d_t, None))
+    ce_k1 = np.zeros_like(ce)
+    check(L.v2m_cuda_memcpy_d2h(ptr(ce_k1), d_t, ce.nbytes))
+    assert np.array_equal(ce, ce_k1), "copy-major matrix from K5 differs from K1 of the edge-major one"
+    ms_k1 = C.c_float()
+    check(L.v2m_cuda_time_transpose_bits(d_ec, h_pad, e_pad, d_t, 5, C.byref(ms_k1)))
+    out["both_orientations"] = {"edge_major_only_s": min(t_one), "both_s": min(t_both), "k1_whole_matrix_ms": ms_k1.value,
+                                "device_resident_estimate_ms": ms.value + ms_k1.value,
+                                "device_resident_estimate_gbs": (alg_bytes + E * h_pad // 8) / ((ms.value + ms_k1.value) * 1e-3) / 1e9,
+                                "identical_to_k1": True}
+    for d in (d_ec, d_ce, d_t):
+        L.v2m_cuda_device_free(d)
+
     if args.cpu_records:
         from oracle import oracle as orc
         rc = min(args.cpu_records, R)

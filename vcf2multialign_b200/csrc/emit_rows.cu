@@ -232,7 +232,7 @@ resolve_rows_kernel(u64 const * __restrict__ lines, u32 const * __restrict__ lin
 // ---------------------------------------------------------------------------------------------------------
 // K2b emit_rows
 // ---------------------------------------------------------------------------------------------------------
-// Persistent CTAs, one per SM: K2P_CWARPS row-writing warps and one staging warp.
+// Persistent CTAs, one per SM: K2P_CWARPS row-writing warps and K2P_SWARPS staging warps.
 //   units   the launch is cut into units of one tile of K2_TCOL aligned columns × rows_per_unit (<= K2P_UNIT_ROWS) rows,
 //           numbered tile-fastest. CTAs draw unit numbers from a ticket counter, so an SM that is served more slowly by
 //           the memory system simply takes fewer units (with a fixed assignment single SMs ran 20 % longer than the
@@ -253,15 +253,14 @@ resolve_rows_kernel(u64 const * __restrict__ lines, u32 const * __restrict__ lin
 // Algorithmic bytes: rows × columns written (+ < 1 % reads). Roofline: HBM write.
 constexpr int K2_EDGE_CAP = 256;								// ALT edge records staged per tile (c2 averages ~100)
 constexpr int K2_LABEL_CAP = 2048;								// label bytes staged per tile (incl. ≤ 15 bytes of alignment slack)
-#ifndef V2M_K2P_CWARPS
-#define V2M_K2P_CWARPS 19
-#endif
-constexpr int K2P_CWARPS = V2M_K2P_CWARPS;						// row warps per CTA: 20 warps in all leave 96 registers per thread (24 would spill)
-constexpr int K2P_THREADS = (K2P_CWARPS + 1) * 32;				// + the staging warp
-#ifndef V2M_K2P_STAGES
-#define V2M_K2P_STAGES 2
-#endif
-constexpr int K2P_STAGES = V2M_K2P_STAGES;						// stage buffers: the staging warp runs up to K2P_STAGES - 1 units ahead
+// Two shapes of the CTA, both 20 warps (5 per scheduler, which leaves 96 registers per thread; 21 warps leave 80 and spill):
+//   19 row warps + 1 staging warp   launches whose units are long (>= K2P_LONG_UNIT rows): the row warps hide the staging, and
+//                                   the 19th row warp is worth ~1 % (c4: 6,526 against 6,472 GB/s);
+//   18 row warps + 2 staging warps  launches of few rows, where a unit is one or two rows per warp and the CTA runs at the
+//                                   staging warps' pace: one memory round trip per unit and staging warp (8-row c4 launch:
+//                                   2.74 -> 4.34 TB/s, 1 row: 0.43 -> 0.80 TB/s).
+constexpr int K2P_MAX_CWARPS = 19;
+constexpr u32 K2P_LONG_UNIT = 48;		// 32-row units: 6.16 TB/s with 18 + 2 against 5.74 with 19 + 1; 64-row units: 6.30 against 6.39
 constexpr u32 K2P_DONE = 0xffffffffu;								// header word 3: no unit left
 constexpr int K2_CHUNKS = K2_TCOL / 512;						// 16-byte chunks of the tile per lane
 constexpr u32 K2_SHORT_PATCH = 16;								// longer spans are written by the whole warp
@@ -280,15 +279,19 @@ struct emit_stage
 	alignas(128) u64		words[K2P_UNIT_ROWS][K2P_WORDS];	// the rows' taken-edge words that cover the tile's edges
 };
 
+// K2P_CWARPS row warps, K2P_SWARPS staging warps (unit k of a CTA is staged by staging warp k % K2P_SWARPS into stage buffer
+// k % K2P_STAGES: each staging warp runs one of its own units ahead).
+template <int K2P_CWARPS, int K2P_SWARPS>
 struct emit_smem
 {
+	static constexpr int K2P_STAGES = 2 * K2P_SWARPS;
 	emit_stage				stage[K2P_STAGES];
 	alignas(128) u8			rows[K2P_CWARPS][2][K2_TCOL];
 	alignas(16) uint4		hdr[K2P_STAGES];	// per stage: tile_edges.x, tile_edges.y, label window base, unit << 2 | words staged? << 1 | edges staged? (K2P_DONE: none)
 	alignas(8) u64			full[K2P_STAGES];	// the stage's copies have landed (transaction bytes)
 	alignas(8) u64			empty[K2P_STAGES];	// every row warp is done with the stage
 };
-static_assert(sizeof(emit_smem) <= 227 * 1024);
+static_assert(sizeof(emit_smem<19, 1>) <= 227 * 1024 && sizeof(emit_smem<18, 2>) <= 227 * 1024);
 
 struct emit_params
 {
@@ -309,11 +312,13 @@ struct emit_params
 	u64				pitch;
 };
 
-__global__ void __launch_bounds__(K2P_THREADS, 1)
+template <int K2P_CWARPS, int K2P_SWARPS>
+__global__ void __launch_bounds__((K2P_CWARPS + K2P_SWARPS) * 32, 1)
 emit_rows_kernel(emit_params const p)
 {
+	constexpr int K2P_STAGES = emit_smem<K2P_CWARPS, K2P_SWARPS>::K2P_STAGES;
 	extern __shared__ __align__(128) u8 smem_raw[];
-	emit_smem &sm(*reinterpret_cast<emit_smem *>(smem_raw));
+	emit_smem<K2P_CWARPS, K2P_SWARPS> &sm(*reinterpret_cast<emit_smem<K2P_CWARPS, K2P_SWARPS> *>(smem_raw));
 
 	unsigned const lane(threadIdx.x & 31), warp(threadIdx.x >> 5);
 	u32 const n_units(p.n_tiles * p.n_row_chunks);
@@ -327,8 +332,12 @@ emit_rows_kernel(emit_params const p)
 	__syncthreads();
 
 	// ---- staging warp: template tile, edge records and labels of the units, one unit ahead of the rows ------------------
-	if (K2P_CWARPS == warp)
+	if (warp >= K2P_CWARPS)
 	{
+		// The units of a CTA form a sequence k = 0, 1, …; staging warp w fills the stages of k = w, w + K2P_SWARPS, … with units
+		// it draws itself. With one staging warp a launch of a few rows (units too short for the row warps to hide the
+		// staging behind) ran at one staging round trip per unit; two warps halve that.
+		u32 const sw(warp - K2P_CWARPS);
 		// Two units ahead of itself: the ticket of unit k + 2 is drawn (one lane's atomic, its result not looked at) while unit
 		// k is staged, and the edge / label ranges of unit k + 1 are loaded while the words of unit k are on their way. The warp
 		// then waits for one memory round trip per unit — the gather — instead of three (ticket, label range, gather), which is
@@ -340,7 +349,7 @@ emit_rows_kernel(emit_params const p)
 		u32 ticket_after(draw_ticket());				// lane 0: the unit after `unit`; read at the top of the next iteration
 		uint2 te(edges_of(unit)), tl(labels_of(unit));
 #pragma unroll 1
-		for (u32 k(0); ; ++k)
+		for (u32 k(sw); ; k += K2P_SWARPS)
 		{
 			u32 const s(k % K2P_STAGES);
 			if (k >= K2P_STAGES) mbar_wait(&sm.empty[s], (k / K2P_STAGES - 1) & 1);		// the rows of unit k - K2P_STAGES are done with this stage
@@ -411,14 +420,27 @@ emit_rows_kernel(emit_params const p)
 	u64 const store_policy(l2_policy_evict_first());		// rows are written once and never read back on the device (+1 %)
 	u32 item(warp);					// this warp's next item in the CTA's flattened (unit, row in unit) sequence
 	u32 n_issued(0);				// rows handed to the TMA engine so far: buffer n_issued & 1 is the one to fill
+	u32 finished(0);				// bit w: staging warp w has run out of units (it posts K2P_DONE once and stops)
 #pragma unroll 1
 	for (u32 k(0); ; ++k)
 	{
 		u32 const s(k % K2P_STAGES);
 		u32 const item_end((k + 1) * RC);
-		mbar_wait(&sm.full[s], (k / K2P_STAGES) & 1);
-		uint4 const hdr(sm.hdr[s]);
-		if (K2P_DONE == hdr.w) break;
+		u32 const sw(k % K2P_SWARPS);
+		bool skip(0 != (finished >> sw & 1u));
+		uint4 hdr(make_uint4(0, 0, 0, K2P_DONE));
+		if (!skip)
+		{
+			mbar_wait(&sm.full[s], (k / K2P_STAGES) & 1);
+			hdr = sm.hdr[s];
+			if (K2P_DONE == hdr.w) { finished |= 1u << sw; skip = true; }
+		}
+		if (skip)
+		{
+			if (finished == (1u << K2P_SWARPS) - 1) break;
+			while (item < item_end) item += K2P_CWARPS;			// this k carries no unit: its item numbers are not used
+			continue;
+		}
 		if (item < item_end)
 		{
 			u32 const unit(hdr.w >> 2);
@@ -651,7 +673,7 @@ int launch_emit_rows(device_graph const &g, u64 const *d_taken, u32 row_begin, u
 	// as well, down to one row per row warp.
 	u32 chunks((n_rows + K2P_UNIT_ROWS - 1) / K2P_UNIT_ROWS);
 	if (u64(p.n_tiles) * chunks < 4 * u64(sms))
-		chunks = std::max<u32>(chunks, std::min<u32>((n_rows + K2P_CWARPS - 1) / K2P_CWARPS, u32((4 * u64(sms) + p.n_tiles - 1) / p.n_tiles)));
+		chunks = std::max<u32>(chunks, std::min<u32>((n_rows + K2P_MAX_CWARPS - 1) / K2P_MAX_CWARPS, u32((4 * u64(sms) + p.n_tiles - 1) / p.n_tiles)));
 	if (char const *env = std::getenv("V2M_K2_UNIT_ROWS"))			// kernel experiments
 		if (int const v = std::atoi(env); v > 0 && v <= K2P_UNIT_ROWS) chunks = (n_rows + u32(v) - 1) / u32(v);
 	p.rows_per_unit = (n_rows + chunks - 1) / chunks;
@@ -660,8 +682,19 @@ int launch_emit_rows(device_graph const &g, u64 const *d_taken, u32 row_begin, u
 	if (n_units * p.rows_per_unit >= (u64(1) << 30)) return fail(1, "too many rows x tiles in one emit_rows launch");
 	if (int const st = unit_tickets(dev, stream, p.tickets)) return st;
 	unsigned const grid(unsigned(std::min<u64>(n_units, u64(sms))));
-	V2M_CUDA_TRY(cudaFuncSetAttribute(emit_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sizeof(emit_smem))));	// per device
-	emit_rows_kernel<<<grid, K2P_THREADS, sizeof(emit_smem), stream>>>(p);
+	bool long_units(p.rows_per_unit >= K2P_LONG_UNIT);
+	if (char const *env = std::getenv("V2M_K2_STAGING_WARPS"))		// kernel experiments: 1 / 2
+		if (int const v = std::atoi(env); 1 == v || 2 == v) long_units = 1 == v;
+	if (long_units)
+	{
+		V2M_CUDA_TRY(cudaFuncSetAttribute(emit_rows_kernel<19, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sizeof(emit_smem<19, 1>))));	// per device
+		emit_rows_kernel<19, 1><<<grid, 20 * 32, sizeof(emit_smem<19, 1>), stream>>>(p);
+	}
+	else
+	{
+		V2M_CUDA_TRY(cudaFuncSetAttribute(emit_rows_kernel<18, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sizeof(emit_smem<18, 2>))));
+		emit_rows_kernel<18, 2><<<grid, 20 * 32, sizeof(emit_smem<18, 2>), stream>>>(p);
+	}
 	V2M_CHECK_LAUNCH("emit_rows_kernel");
 	return 0;
 }
