@@ -441,6 +441,8 @@ def main():
         if shard:
             h2d -= int(paths_ec.nbytes) - int(g.e_pad * ((int(copies.max()) + 64) // 64 - int(copies.min()) // 64) * 8)
 
+        setup_s = []
+
         def e2e_step(row_limit=None):
             if shard:
                 # this rank's slab of the path matrix only (cut out of the host matrix inside the timed step)
@@ -448,8 +450,10 @@ def main():
                 local_idx = np.where(rows_idx == v2m.PLOIDY_MAX, rows_idx, rows_idx - np.uint32(off)).astype(np.uint32)
             else:
                 sg, local_idx = g, rows_idx
+            t_step = time.perf_counter()
             dg = v2m.DeviceGraph(sg, w.ref)                       # H2D of the graph + K1 transpose + template
             pl = dg.plan_haplotypes(local_idx)                    # K2a
+            setup_s.append(time.perf_counter() - t_step)
             for r0 in range(0, row_limit or n_rows, e2e_block):   # K2b → pinned host
                 check(L.v2m_cuda_emit_rows(pl._p, r0, min(n_rows, r0 + e2e_block), 0, A, h_out, pitch))
             pl.close()
@@ -475,11 +479,11 @@ def main():
         link_peak = world * copy_bytes * iters / t_copy / 1e9
         e2e_value = total_rows * A * args.e2e_steps / t_e2e / 1e9
         e2e = {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-               "steps": args.e2e_steps, "s_per_step": t_e2e / args.e2e_steps,
+               "steps": args.e2e_steps, "s_per_step": t_e2e / args.e2e_steps, "setup_s_per_step": float(np.mean(setup_s[1:])) if len(setup_s) > 1 else None,
                "peak": link_peak, "peak_unit": "GB/s", "frac": e2e_value / link_peak,
                "peak_source": f"measured live on this box: plain cudaMemcpyAsync D2H into pinned memory, {copy_bytes} B per pass in 256 MiB pieces on two streams, "
                               f"{iters} passes, all {world} rank(s) copying at once (sum over ranks / slowest rank); 1 byte crosses the link per base",
-               "note": "graph upload (host arrays" + ("; this rank's slab of the path matrix, sharding.shard_graph" if shard else "") + ") + K1 + K2a + K2b with this rank's rows copied into pinned host memory; full job per step; byte counts are per rank"}
+               "note": "setup_s_per_step = graph upload (host arrays" + ("; this rank's slab of the path matrix, sharding.shard_graph" if shard else "") + ") + K1 + K2a + K2b with this rank's rows copied into pinned host memory; full job per step; byte counts are per rank"}
         L.v2m_cuda_host_free(h_out)
         g.paths_by_edge_and_chrom_copy = None
 

@@ -889,3 +889,60 @@ def test_graph_without_reference_serves_the_sweeps(v2m, tmp_path):
     assert rows[0].tobytes() == og.output_sequence(0) and rows[1].tobytes() == og.output_sequence(orc.PLOIDY_MAX)
     un = plan.emit_rows_unaligned()
     assert un[0] == og.output_sequence(0, None, True)
+
+
+def test_device_writers_stay_inside_their_buffers(v2m, tmp_path):
+    """compute-sanitizer is closed on this GPU pool, so the writers' bounds are checked with guard bytes instead: emit_rows
+    (bulk stores + ragged tails, aligned and unaligned windows) must not touch the bytes before the buffer, after it, or
+    between a row's last column and the next row; the three transpose kernels must not touch what surrounds their destination."""
+    import ctypes as C
+    from vcf2multialign_b200._lib import check, lib, ptr
+    L = lib()
+    GUARD = 4096
+    og = rg.random_oracle_graph(str(tmp_path), 4242, ref_len=30000, n_records=2200, n_samples=35, ploidy=2, long_del_prob=0.03)
+    a = dict(og.arrays()); a["paths_ce"] = None
+    g = v2m.VariantGraph.from_arrays(a)
+    dg = v2m.DeviceGraph(g, og.arrays()["ref"])
+    H, A = g.total_chromosome_copies(), g.aligned_length()
+    idx = list(range(H)) + [orc.PLOIDY_MAX]
+    plan = dg.plan_haplotypes(idx)
+    full = [og.output_sequence(h) for h in idx]
+    for c0, c1 in ((0, A), (4096 * 2 + 16, A - 3), (16, 4096 * 3 + 5), (4096, 4096 * 2)):
+        width = c1 - c0
+        pitch = int(L.v2m_cuda_row_pitch(width))
+        n = len(idx)
+        total = 2 * GUARD + n * pitch
+        host = np.full(total, 0xEE, np.uint8)
+        d = L.v2m_cuda_device_alloc(total)
+        assert d
+        check(L.v2m_cuda_memcpy_h2d(d, ptr(host), total))
+        check(L.v2m_cuda_emit_rows_device(plan._p, 0, n, c0, c1, C.c_void_p(d + GUARD), pitch, None))
+        check(L.v2m_cuda_synchronize())
+        check(L.v2m_cuda_memcpy_d2h(ptr(host), d, total))
+        L.v2m_cuda_device_free(d)
+        assert (host[:GUARD] == 0xEE).all() and (host[GUARD + n * pitch:] == 0xEE).all(), (c0, c1)
+        body = host[GUARD : GUARD + n * pitch].reshape(n, pitch)
+        assert (body[:, width:] == 0xEE).all(), (c0, c1)
+        for i in range(n):
+            assert body[i, :width].tobytes() == full[i][c0:c1], (c0, c1, i)
+    plan.close(); dg.close()
+
+    rng = np.random.default_rng(8)
+    for kernel in ("0", "1", "2"):
+        for rows, cols in ((1088, 3264), (576, 5184), (1280, 20928)):
+            os.environ["V2M_K1_TALL"] = kernel
+            try:
+                src = rng.integers(0, 2**64, rows * cols // 64, dtype=np.uint64)
+                nbytes = rows * cols // 8
+                host = np.full(2 * GUARD + nbytes, 0xEE, np.uint8)
+                d_src, d = L.v2m_cuda_device_alloc(nbytes), L.v2m_cuda_device_alloc(host.size)
+                check(L.v2m_cuda_memcpy_h2d(d_src, ptr(src), nbytes))
+                check(L.v2m_cuda_memcpy_h2d(d, ptr(host), host.size))
+                check(L.v2m_cuda_transpose_bits_device(d_src, rows, cols, C.c_void_p(d + GUARD), None))
+                check(L.v2m_cuda_synchronize())
+                check(L.v2m_cuda_memcpy_d2h(ptr(host), d, host.size))
+                L.v2m_cuda_device_free(d_src); L.v2m_cuda_device_free(d)
+                assert (host[:GUARD] == 0xEE).all() and (host[GUARD + nbytes:] == 0xEE).all(), (kernel, rows, cols)
+                assert np.array_equal(host[GUARD : GUARD + nbytes].view(np.uint64), orc.transpose(src, rows, cols)), (kernel, rows, cols)
+            finally:
+                os.environ.pop("V2M_K1_TALL", None)

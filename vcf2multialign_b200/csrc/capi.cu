@@ -558,7 +558,7 @@ int v2m_cuda_emit_rows(v2m_plan_t p, uint32_t row_begin, uint32_t row_end, uint6
 	u64 const skip(col_begin - cb);
 	u64 const width(col_end - col_begin);
 	u64 const d_pitch(device_row_pitch(col_end - cb));
-	u64 const budget(u64(256) << 20);	// bytes per staging buffer
+	static u64 const budget([] { char const *env(std::getenv("V2M_STAGE_MIB")); u64 const v(env ? std::strtoull(env, nullptr, 10) : 0); return (v ? v : u64(256)) << 20; }());	// bytes per staging buffer (experiments: V2M_STAGE_MIB)
 	u32 const chunk_rows(u32(std::max<u64>(1, std::min<u64>(row_end - row_begin, budget / d_pitch))));
 
 	// Staging tiles and streams are kept per host thread: a caller streaming a plan block by block (bench.py's end-to-end leg,
