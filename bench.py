@@ -15,7 +15,9 @@ device times only). `--scaling weak` gives every rank its own 5,008-haplotype co
 `value` is device-resident (rows written into an HBM ring of two row blocks that is overwritten); `e2e` runs the same job
 through the C ABI with host buffers: graph arrays uploaded from host memory, K1, K2a, K2b, every row copied into pinned host
 memory, all inside the timed region, and is reported as a fraction of the host link's own ceiling — plain cudaMemcpyAsync
-device-to-host copies, measured live on the same box with all ranks copying at once (`e2e.peak`).
+device-to-host copies, measured live on the same box with all ranks copying at once (`e2e.peak`). At N > 1 the e2e leg
+hands the job's rows out in blocks from a shared counter (sharding.RowBlockQueue; still no collective): the GPUs of a box do
+not all get the same share of the host link, and static equal ranges would wait for the slowest one.
 
 `--workload c5` prints the transpose_matrix microbench line (K1 on a 5056 × 6,000,000 bit matrix, GB/s against the HBM
 roofline) instead. `--impl reference` times the reference's CPU implementation of the path — its restatement in oracle/
@@ -154,6 +156,15 @@ def barrier(dist, local):
         import torch
         dist.barrier(device_ids=[local])
         torch.cuda.synchronize()
+
+
+def sum_over_ranks(dist, local, x: float) -> float:
+    if dist is None:
+        return x
+    import torch
+    t = torch.tensor([x], dtype=torch.float64, device=torch.device("cuda", local))
+    dist.all_reduce(t, op=dist.ReduceOp.SUM)
+    return float(t.item())
 
 
 def max_over_ranks(dist, local, x: float) -> float:
@@ -434,56 +445,79 @@ def main():
         g.paths_by_edge_and_chrom_copy = paths_ec
         h2d = int(paths_ec.nbytes + w.ref.nbytes + g.reference_positions.nbytes + g.aligned_positions.nbytes + g.alt_edge_targets.nbytes
                   + g.alt_edge_count_csum.nbytes + g.label_offsets.nbytes + len(g.label_chars) + rows_idx.nbytes)
-        d2h = int(n_rows * A)
 
-        shard = args.scaling == "strong" and world > 1
-        copies = rows_idx[rows_idx != v2m.PLOIDY_MAX]
-        if shard:
-            h2d -= int(paths_ec.nbytes) - int(g.e_pad * ((int(copies.max()) + 64) // 64 - int(copies.min()) // 64) * 8)
-
-        setup_s = []
+        # N > 1, strong scaling: the rows of the ONE job are handed out in blocks as the ranks ask for them (sharding.RowBlockQueue:
+        # a counter under /dev/shm, control plane only). The host link is not the same for every GPU of a box — with all eight
+        # copying at once a plain D2H copy runs at 8 to 18 GB/s per GPU here — so equal static row ranges leave the stream waiting
+        # for the rank behind the slowest link (profiles/r02_n_bench_c4_n8_static_shards.json: 88 Gbase/s). Any rank can produce
+        # any row block, so every rank uploads the whole graph and plans every row.
+        dynamic = args.scaling == "strong" and world > 1
+        step_rows = rows_all if dynamic else rows_idx
+        n_step_rows = int(step_rows.size)
+        queue = None
+        if dynamic:
+            queue = sharding.RowBlockQueue(f"/dev/shm/v2m_bench_rows_{os.environ.get('MASTER_PORT', '0')}", n_step_rows, e2e_block)
+            h2d += int(rows_all.nbytes - rows_idx.nbytes)
+        setup_s, rows_done = [], []
 
         def e2e_step(row_limit=None):
-            if shard:
-                # this rank's slab of the path matrix only (cut out of the host matrix inside the timed step)
-                sg, off = sharding.shard_graph(g, int(copies.min()), int(copies.max()) + 1)
-                local_idx = np.where(rows_idx == v2m.PLOIDY_MAX, rows_idx, rows_idx - np.uint32(off)).astype(np.uint32)
-            else:
-                sg, local_idx = g, rows_idx
             t_step = time.perf_counter()
-            dg = v2m.DeviceGraph(sg, w.ref)                       # H2D of the graph + K1 transpose + template
-            pl = dg.plan_haplotypes(local_idx)                    # K2a
+            dg = v2m.DeviceGraph(g, w.ref)                        # H2D of the graph + K1 transpose + template
+            pl = dg.plan_haplotypes(step_rows)                    # K2a
             setup_s.append(time.perf_counter() - t_step)
-            for r0 in range(0, row_limit or n_rows, e2e_block):   # K2b → pinned host
-                check(L.v2m_cuda_emit_rows(pl._p, r0, min(n_rows, r0 + e2e_block), 0, A, h_out, pitch))
+            done = 0
+            if row_limit is not None or not dynamic:
+                for r0 in range(0, row_limit or n_step_rows, e2e_block):                                   # K2b → pinned host
+                    check(L.v2m_cuda_emit_rows(pl._p, r0, min(n_step_rows, r0 + e2e_block), 0, A, h_out, pitch))
+                    done += min(n_step_rows, r0 + e2e_block) - r0
+            else:
+                while True:
+                    blk = queue.next()
+                    if blk is None:
+                        break
+                    check(L.v2m_cuda_emit_rows(pl._p, blk[0], blk[1], 0, A, h_out, pitch))
+                    done += blk[1] - blk[0]
+            rows_done.append(done)
             pl.close()
             dg.close()
 
-        e2e_step(min(n_rows, 2 * e2e_block))                      # warm-up: every allocation, page-locking and code path of a step, two blocks of rows
-        barrier(dist, local)
-        t0 = time.perf_counter()
+        e2e_step(min(n_step_rows, 2 * e2e_block))                 # warm-up: every allocation, page-locking and code path of a step, two blocks of rows
+        t_e2e = 0.0
         for _ in range(args.e2e_steps):
+            if dynamic:
+                barrier(dist, local)
+                if rank == 0:
+                    queue.reset()
+            barrier(dist, local)
+            t0 = time.perf_counter()
             e2e_step()
-        check(L.v2m_cuda_synchronize())
-        t_e2e = max_over_ranks(dist, local, time.perf_counter() - t0)
+            check(L.v2m_cuda_synchronize())
+            t_e2e += max_over_ranks(dist, local, time.perf_counter() - t0)
         barrier(dist, local)
-        # The host link's own ceiling on this box: plain D2H copies of the same row blocks (256 MiB pieces, two streams), every rank at once.
+        if queue is not None:
+            queue.close()
+        d2h = int(rows_done[-1] * A)
+        # The host link's own ceiling on this box: plain D2H copies of the same row blocks (256 MiB pieces, two streams), every rank
+        # copying at once for ~3 s; the ceiling is the sum of the ranks' rates.
         copy_bytes = int(min(e2e_block, block) * pitch)
         secs = C.c_double()
-        check(L.v2m_cuda_time_d2h_copies(h_out, ring[0], copy_bytes, 256 << 20, 1, C.byref(secs)))
-        iters = int(max(2, min(200, 3.0 / max(secs.value, 1e-4))))
+        barrier(dist, local)
+        check(L.v2m_cuda_time_d2h_copies(h_out, ring[0], copy_bytes, 256 << 20, 2, C.byref(secs)))      # calibration, all ranks at once
+        iters = int(max(2, min(400, 3.0 / max(secs.value / 2, 1e-4))))
         barrier(dist, local)
         check(L.v2m_cuda_time_d2h_copies(h_out, ring[0], copy_bytes, 256 << 20, iters, C.byref(secs)))
-        t_copy = max_over_ranks(dist, local, float(secs.value))
+        rank_gbs = copy_bytes * iters / float(secs.value) / 1e9
+        link_peak = sum_over_ranks(dist, local, rank_gbs)
         barrier(dist, local)
-        link_peak = world * copy_bytes * iters / t_copy / 1e9
         e2e_value = total_rows * A * args.e2e_steps / t_e2e / 1e9
         e2e = {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                "steps": args.e2e_steps, "s_per_step": t_e2e / args.e2e_steps, "setup_s_per_step": float(np.mean(setup_s[1:])) if len(setup_s) > 1 else None,
                "peak": link_peak, "peak_unit": "GB/s", "frac": e2e_value / link_peak,
                "peak_source": f"measured live on this box: plain cudaMemcpyAsync D2H into pinned memory, {copy_bytes} B per pass in 256 MiB pieces on two streams, "
-                              f"{iters} passes, all {world} rank(s) copying at once (sum over ranks / slowest rank); 1 byte crosses the link per base",
-               "note": "setup_s_per_step = graph upload (host arrays" + ("; this rank's slab of the path matrix, sharding.shard_graph" if shard else "") + ") + K1 + K2a + K2b with this rank's rows copied into pinned host memory; full job per step; byte counts are per rank"}
+                              f"~3 s per rank, all {world} rank(s) copying at once, sum of the ranks' rates (rank 0: {rank_gbs:.1f} GB/s); 1 byte crosses the link per base",
+               "row_assignment": (f"dynamic: blocks of {e2e_block} rows drawn from a shared counter by {world} ranks (rank 0 took {rows_done[-1]} rows)" if dynamic
+                                  else "static: this rank's rows in order"),
+               "note": "setup_s_per_step = graph upload (host arrays) + K1 + K2a; then K2b with the rows copied into pinned host memory; full job per step; byte counts are rank 0's"}
         L.v2m_cuda_host_free(h_out)
         g.paths_by_edge_and_chrom_copy = None
 

@@ -132,3 +132,38 @@ def test_shard_graph_rows_equal_cohort_rows():
         og = oracle_graph(sub)
         for c in {begin, (begin + end) // 2, end - 1}:
             assert og.output_sequence(c - off) == full.output_sequence(c), (begin, end, c)
+
+
+def _take_blocks(path, n_rows, block_rows, out_q):
+    from vcf2multialign_b200 import sharding
+    q = sharding.RowBlockQueue(path, n_rows, block_rows)
+    got = []
+    while True:
+        b = q.next()
+        if b is None:
+            break
+        got.append(b)
+    q.close()
+    out_q.put(got)
+
+
+def test_row_block_queue_hands_every_block_out_once(tmp_path):
+    """sharding.RowBlockQueue: several processes draw row blocks from one counter; every block is taken exactly once."""
+    import multiprocessing as mp
+    from vcf2multialign_b200 import sharding
+    path = str(tmp_path / "queue")
+    q0 = sharding.RowBlockQueue(path, 5009, 8)
+    q0.reset()
+    ctx = mp.get_context("spawn")
+    out = ctx.Queue()
+    procs = [ctx.Process(target=_take_blocks, args=(path, 5009, 8, out)) for _ in range(3)]
+    for p in procs:
+        p.start()
+    taken = [b for _ in procs for b in out.get(timeout=120)]
+    for p in procs:
+        p.join(timeout=60)
+    assert sorted(taken) == [(b, min(5009, b + 8)) for b in range(0, 5009, 8)]
+    assert q0.next() is None
+    q0.reset()
+    assert q0.next() == (0, 8)
+    q0.close()

@@ -46,6 +46,47 @@ def shard_graph(graph, copy_begin: int, copy_end: int):
     return sub, 64 * w0
 
 
+class RowBlockQueue:
+    """Row blocks handed out to the ranks of one box as they ask for them (control plane only: a counter in a small file that
+    every rank can open, e.g. under /dev/shm, advanced under an fcntl lock — no collective, nothing on the data path).
+
+    Why: the host link is not the same for every GPU of a box (on this pool's 8-GPU boxes a plain D2H copy runs at 8 – 18 GB/s
+    per GPU when all eight copy at once, profiles/r02_d2h_ceiling.txt), so with equal static row ranges the whole stream waits
+    for the rank behind the slowest link. Every aligned row has the same length and its place in the A2M stream is known up
+    front (row_offsets), so any rank can produce any block."""
+
+    def __init__(self, path: str, n_rows: int, block_rows: int):
+        import fcntl
+        self._fcntl = fcntl
+        self.path, self.n_rows, self.block_rows = path, int(n_rows), int(block_rows)
+        self.n_blocks = (self.n_rows + self.block_rows - 1) // self.block_rows
+        self.fd = os.open(path, os.O_RDWR | os.O_CREAT, 0o600)
+
+    def reset(self):
+        """Called by ONE rank before the others start taking blocks (callers put a barrier after it)."""
+        os.pwrite(self.fd, (0).to_bytes(8, "little"), 0)
+
+    def next(self):
+        """The next block's row range (begin, end), or None when all blocks have been taken."""
+        f = self._fcntl
+        f.lockf(self.fd, f.LOCK_EX, 8, 0)
+        try:
+            raw = os.pread(self.fd, 8, 0)
+            b = int.from_bytes(raw, "little") if len(raw) == 8 else 0
+            if b >= self.n_blocks:
+                return None
+            os.pwrite(self.fd, (b + 1).to_bytes(8, "little"), 0)
+        finally:
+            f.lockf(self.fd, f.LOCK_UN, 8, 0)
+        begin = b * self.block_rows
+        return begin, min(self.n_rows, begin + self.block_rows)
+
+    def close(self):
+        if self.fd is not None:
+            os.close(self.fd)
+            self.fd = None
+
+
 def row_offsets(ids, lengths) -> np.ndarray:
     """Byte offset of every row's '>' in the stream, plus the total size as the last entry."""
     sizes = np.array([1 + len(i.encode()) + 1 + int(n) + 1 for i, n in zip(ids, lengths)], np.int64)
