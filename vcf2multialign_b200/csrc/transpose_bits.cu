@@ -234,7 +234,9 @@ transpose_bits_tall_kernel(u64 const * __restrict__ src, u32 * __restrict__ dst,
 //   `math pipe throttle` is the top stall (1.16 G warp instructions against the tile kernel's 0.77 G): with the stores out of
 //   the way the transpose is bound by its own integer work — 64 PRMT + 144 LOP3 / SHF for the bit stages plus index
 //   arithmetic, selects for the swizzle and the lane swap — and the shear and the halo add to exactly that. It therefore stays
-//   opt-in (V2M_K1_TALL=2) as the record of the experiment; the launcher's default is unchanged.
+//   opt-in (V2M_K1_TALL=2) as the record of the experiment; the launcher's default is unchanged. The same shear on the 512-line
+//   × 1024-bit tile kernel (128-byte source pieces, the cheapest tiling) ran 2.02 ms on c5 with 32-bit stores and 1.92 ms with
+//   the lane swap, 2.26 ms on the c4 shape: the 37 % halo and the shear cost more than the aligned 64-byte runs give back.
 //   (3) tiles are independent, two CTAs per SM, row bands fastest in the grid, so that at any moment the CTAs in flight write
 //       ~30 consecutive runs (3.8 KB) of every destination line. A variant in which persistent CTAs walked along the lines and
 //       carried each line's last bytes from tile to tile in shared memory (no halo, no shear) ran 2.50 ms on c5 against the
