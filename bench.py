@@ -457,12 +457,19 @@ def main():
         queue = None
         if dynamic:
             queue = sharding.RowBlockQueue(f"/dev/shm/v2m_bench_rows_{os.environ.get('MASTER_PORT', '0')}", n_step_rows, e2e_block)
-            h2d += int(rows_all.nbytes - rows_idx.nbytes)
+            h2d += int(rows_all.nbytes - rows_idx.nbytes) - (int(paths_ec.nbytes) if rank != 0 else 0)
         setup_s, rows_done = [], []
 
         def e2e_step(row_limit=None):
             t_step = time.perf_counter()
-            dg = v2m.DeviceGraph(g, w.ref)                        # H2D of the graph + K1 transpose + template
+            if dynamic:
+                # one upload of the path matrix per box (rank 0), the other ranks fetch it over NVLink; everything else of the
+                # graph (0.6 GB) goes up from every rank's own host arrays
+                t_paths = sharding.replicate_path_matrix(dist, local, paths_ec if rank == 0 else None, path_bytes // 8)
+                dg = v2m.DeviceGraph(g, w.ref, d_paths_by_edge_and_chrom_copy=t_paths.data_ptr())
+                del t_paths
+            else:
+                dg = v2m.DeviceGraph(g, w.ref)                    # H2D of the graph + K1 transpose + template
             pl = dg.plan_haplotypes(step_rows)                    # K2a
             setup_s.append(time.perf_counter() - t_step)
             done = 0
@@ -517,7 +524,7 @@ def main():
                               f"~3 s per rank, all {world} rank(s) copying at once, sum of the ranks' rates (rank 0: {rank_gbs:.1f} GB/s); 1 byte crosses the link per base",
                "row_assignment": (f"dynamic: blocks of {e2e_block} rows drawn from a shared counter by {world} ranks (rank 0 took {rows_done[-1]} rows)" if dynamic
                                   else "static: this rank's rows in order"),
-               "note": "setup_s_per_step = graph upload (host arrays) + K1 + K2a; then K2b with the rows copied into pinned host memory; full job per step; byte counts are rank 0's"}
+               "note": "setup_s_per_step = graph upload (host arrays" + ("; the path matrix uploaded by rank 0 and fetched over NVLink by the others" if dynamic else "") + ") + K1 + K2a; then K2b with the rows copied into pinned host memory; full job per step; byte counts are rank 0's"}
         L.v2m_cuda_host_free(h_out)
         g.paths_by_edge_and_chrom_copy = None
 

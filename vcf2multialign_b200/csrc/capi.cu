@@ -194,6 +194,14 @@ int v2m_cuda_graph_upload(const v2m_graph_view *view, v2m_graph_t *out)
 	auto holder(std::make_unique<v2m_graph_s>());
 	device_graph &g(holder->g);
 	V2M_CUDA_TRY(cudaGetDevice(&g.device));
+	bool const trace(nullptr != std::getenv("V2M_TRACE"));		// host-side phase times on stderr
+	auto mark([&, t_last = std::chrono::steady_clock::now()](char const *what) mutable {
+		if (!trace) return;
+		cudaDeviceSynchronize();
+		auto const now(std::chrono::steady_clock::now());
+		std::fprintf(stderr, "[graph_upload] %-32s %8.2f ms\n", what, std::chrono::duration<double, std::milli>(now - t_last).count());
+		t_last = now;
+	});
 	g.N = N; g.E = E; g.L = view->ref_seq ? view->ref_len : 0; g.A = A;
 	g.h_pad = view->h_pad; g.e_pad = view->e_pad; g.Wh = g.h_pad / 64; g.We = g.e_pad / 64;
 	g.H = view->total_chromosome_copies;
@@ -241,6 +249,7 @@ int v2m_cuda_graph_upload(const v2m_graph_view *view, v2m_graph_t *out)
 		for (u64 e(lb); e < rb; ++e) reach = std::max<u64>(reach, view->alt_edge_targets[e]);
 	}
 	g.label_bytes = E ? view->label_offsets[E] : 0;
+	mark("host copies + node / edge arrays");
 
 	// Per tile of K2_TCOL positions (aligned columns / reference positions): the edges whose span may intersect it.
 	auto const tile_edge_ranges([E](u64 const n_tiles, auto const &span /* e → (begin, end) */) {
@@ -283,7 +292,9 @@ int v2m_cuda_graph_upload(const v2m_graph_view *view, v2m_graph_t *out)
 	if (int const st = dev_upload(g.tile_edges, tile_edges.data(), tile_edges.size())) return st;
 	if (int const st = dev_upload(g.tile_labels, tile_labels.data(), tile_labels.size())) return st;
 	if (int const st = dev_upload(g.edge_ref, edge_ref.data(), g.e_pad)) return st;
+	mark("tile tables");
 	if (int const st = dev_upload(g.ref_tile_edges, ref_tile_edges.data(), ref_tile_edges.size())) return st;
+	mark("uploads of the small arrays");
 
 	u64 const path_words(g.Wh * g.e_pad);
 	if (path_words)
@@ -308,11 +319,13 @@ int v2m_cuda_graph_upload(const v2m_graph_view *view, v2m_graph_t *out)
 			if (int const st = launch_transpose_bits(g.paths_he, g.e_pad, g.h_pad, g.paths_eh, nullptr)) return st;
 	}
 
+	mark("path matrices (upload / K1)");
 	// Without a reference the graph serves the sweeps (find_cut_positions, find_matchings, segment_classes) and plans; rows
 	// need v2m_cuda_graph_attach_reference first.
 	if (view->ref_seq)
 		if (int const st = attach_reference(*holder, view->ref_seq, view->ref_len)) return st;
 	V2M_CUDA_TRY(cudaDeviceSynchronize());
+	mark("reference + template");
 	*out = holder.release();
 	return V2M_OK;
 }

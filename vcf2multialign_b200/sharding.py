@@ -87,6 +87,22 @@ class RowBlockQueue:
             self.fd = None
 
 
+def replicate_path_matrix(dist, device_index: int, words, n_words: int, src: int = 0):
+    """The edge-major path matrix on every GPU of the box with ONE host-to-device upload: rank `src` uploads its host words,
+    the other ranks receive them over NVLink (one NCCL broadcast — replication of the job's input, not a collective on the
+    row data path; SURVEY §5 names it as the alternative to N uploads through the shared host link). Returns a torch int64
+    tensor on cuda:device_index whose data_ptr() goes into DeviceGraph(d_paths_by_edge_and_chrom_copy=…)."""
+    import torch
+    dev = torch.device("cuda", device_index)
+    if dist.get_rank() == src:
+        t = torch.from_numpy(np.ascontiguousarray(words).view(np.int64)).to(dev)
+    else:
+        t = torch.empty(int(n_words), dtype=torch.int64, device=dev)
+    dist.broadcast(t, src=src)
+    torch.cuda.synchronize(dev)
+    return t
+
+
 def row_offsets(ids, lengths) -> np.ndarray:
     """Byte offset of every row's '>' in the stream, plus the total size as the last entry."""
     sizes = np.array([1 + len(i.encode()) + 1 + int(n) + 1 for i, n in zip(ids, lengths)], np.int64)
