@@ -457,15 +457,17 @@ def main():
         queue = None
         if dynamic:
             queue = sharding.RowBlockQueue(f"/dev/shm/v2m_bench_rows_{os.environ.get('MASTER_PORT', '0')}", n_step_rows, e2e_block)
-            h2d += int(rows_all.nbytes - rows_idx.nbytes) - (int(paths_ec.nbytes) if rank != 0 else 0)
+            h2d += int(rows_all.nbytes - rows_idx.nbytes) - int(paths_ec.nbytes) * (world - 1) // world
         setup_s, rows_done = [], []
 
         def e2e_step(row_limit=None):
             t_step = time.perf_counter()
             if dynamic:
-                # one upload of the path matrix per box (rank 0), the other ranks fetch it over NVLink; everything else of the
-                # graph (0.6 GB) goes up from every rank's own host arrays
-                t_paths = sharding.replicate_path_matrix(dist, local, paths_ec if rank == 0 else None, path_bytes // 8)
+                # one pass of the path matrix over the host link per box: every rank uploads 1 / N of it and the ranks exchange the
+                # slices over NVLink; everything else of the graph (0.6 GB) goes up from every rank's own host arrays
+                t_paths = sharding.replicate_path_matrix(dist, local, paths_ec, path_bytes // 8)
+                if row_limit is not None:                         # warm-up step: the replica is the host matrix (wrapping 64-bit sums agree)
+                    assert int(t_paths.sum().item()) == int(paths_ec.view(np.int64).sum()), "replicated path matrix differs from the host matrix"
                 dg = v2m.DeviceGraph(g, w.ref, d_paths_by_edge_and_chrom_copy=t_paths.data_ptr())
                 del t_paths
             else:
@@ -524,7 +526,7 @@ def main():
                               f"~3 s per rank, all {world} rank(s) copying at once, sum of the ranks' rates (rank 0: {rank_gbs:.1f} GB/s); 1 byte crosses the link per base",
                "row_assignment": (f"dynamic: blocks of {e2e_block} rows drawn from a shared counter by {world} ranks (rank 0 took {rows_done[-1]} rows)" if dynamic
                                   else "static: this rank's rows in order"),
-               "note": "setup_s_per_step = graph upload (host arrays" + ("; the path matrix uploaded by rank 0 and fetched over NVLink by the others" if dynamic else "") + ") + K1 + K2a; then K2b with the rows copied into pinned host memory; full job per step; byte counts are rank 0's"}
+               "note": "setup_s_per_step = graph upload (host arrays" + ("; every rank uploads 1 / N of the path matrix and the slices are exchanged over NVLink" if dynamic else "") + ") + K1 + K2a; then K2b with the rows copied into pinned host memory; full job per step; byte counts are rank 0's"}
         L.v2m_cuda_host_free(h_out)
         g.paths_by_edge_and_chrom_copy = None
 

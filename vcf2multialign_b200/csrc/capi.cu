@@ -859,6 +859,8 @@ static int stream_a2m_impl(v2m_plan_t p, const char *ids, int unaligned, v2m_sin
 	u64 const max_len(*std::max_element(lengths.begin(), lengths.end()));
 	u64 const pitch(device_row_pitch(max_len));
 	u32 const block_rows(u32(std::max<u64>(1, std::min<u64>(n_rows, (u64(256) << 20) / pitch))));
+	staging_area &thread_streams(thread_staging());
+	if (int const rc = thread_streams.reserve(0)) return rc;
 	file_mapping mapping;
 	bool positional(false);
 	if (positional_fd >= 0)
@@ -895,7 +897,7 @@ static int stream_a2m_impl(v2m_plan_t p, const char *ids, int unaligned, v2m_sin
 		{
 			if (cudaSuccess != cudaMallocHost(reinterpret_cast<void **>(&h_buf[i]), u64(block_rows) * pitch)) { st = fail(V2M_ERR_CUDA, "write_a2m: cudaMallocHost failed"); break; }
 			if ((st = dev_alloc(d_buf[i], u64(block_rows) * pitch))) break;
-			if (cudaSuccess != cudaStreamCreateWithFlags(&streams[i], cudaStreamNonBlocking)) st = fail(V2M_ERR_CUDA, "write_a2m: cudaStreamCreate failed");
+			streams[i] = thread_streams.streams[i];		// the calling thread's two streams: no stream (and no unit ticket for it) is created per call
 		}
 		if (st) break;
 		if (unaligned)
@@ -966,7 +968,7 @@ static int stream_a2m_impl(v2m_plan_t p, const char *ids, int unaligned, v2m_sin
 
 	for (int i(0); i < 2; ++i)
 	{
-		if (streams[i]) { cudaStreamSynchronize(streams[i]); cudaStreamDestroy(streams[i]); }
+		if (streams[i]) cudaStreamSynchronize(streams[i]);
 		cudaFree(d_buf[i]);
 		if (h_buf[i]) cudaFreeHost(h_buf[i]);
 	}

@@ -87,20 +87,24 @@ class RowBlockQueue:
             self.fd = None
 
 
-def replicate_path_matrix(dist, device_index: int, words, n_words: int, src: int = 0):
-    """The edge-major path matrix on every GPU of the box with ONE host-to-device upload: rank `src` uploads its host words,
-    the other ranks receive them over NVLink (one NCCL broadcast — replication of the job's input, not a collective on the
-    row data path; SURVEY §5 names it as the alternative to N uploads through the shared host link). Returns a torch int64
-    tensor on cuda:device_index whose data_ptr() goes into DeviceGraph(d_paths_by_edge_and_chrom_copy=…)."""
+def replicate_path_matrix(dist, device_index: int, words, n_words: int):
+    """The edge-major path matrix on every GPU of the box with ONE host-to-device pass over it: every rank uploads its 1 / N
+    slice of the host words and the ranks exchange the slices over NVLink (one NCCL all-gather — replication of the job's
+    input, not a collective on the row data path; SURVEY §5 names it as the alternative to N full uploads through the shared
+    host link). `words`: the host matrix (every rank has it; only the rank's own slice is read). Returns a torch int64 tensor
+    on cuda:device_index whose data_ptr() goes into DeviceGraph(d_paths_by_edge_and_chrom_copy=…)."""
     import torch
     dev = torch.device("cuda", device_index)
-    if dist.get_rank() == src:
-        t = torch.from_numpy(np.ascontiguousarray(words).view(np.int64)).to(dev)
-    else:
-        t = torch.empty(int(n_words), dtype=torch.int64, device=dev)
-    dist.broadcast(t, src=src)
+    rank, world = dist.get_rank(), dist.get_world_size()
+    per = (int(n_words) + world - 1) // world
+    full = torch.empty(per * world, dtype=torch.int64, device=dev)
+    lo, hi = min(n_words, rank * per), min(n_words, (rank + 1) * per)
+    part = full[rank * per : (rank + 1) * per]
+    if hi > lo:
+        part[: hi - lo].copy_(torch.from_numpy(np.ascontiguousarray(words[lo:hi]).view(np.int64)))
+    dist.all_gather_into_tensor(full, part.clone())
     torch.cuda.synchronize(dev)
-    return t
+    return full[: int(n_words)]
 
 
 def row_offsets(ids, lengths) -> np.ndarray:
