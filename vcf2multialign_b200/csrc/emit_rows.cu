@@ -14,7 +14,7 @@
 //   build_template_kernel   REF-aligned template, A bytes, once per graph.
 //   compose_founder_kernel  path bits of founder rows: per segment the bits of the assigned chromosome copy
 //                           (founder_sequence_writing_delegate::handle_node, founder_…cc:106-114).
-//   resolve_rows_kernel     K2a: path bits → taken bits, one warp per row, 8192 edges per step; per-edge loads only for set
+//   resolve_rows_kernel     K2a: path bits → taken bits, one warp per row, 16,384 edges per step; per-edge loads only for set
 //                           bits of edges that an earlier edge can reach over.
 //   emit_rows_kernel        K2b: rows × columns tile writer, persistent CTAs; template tile + edge records staged in shared
 //                           memory by bulk async copies one tile ahead, rows assembled in shared memory and written by
@@ -149,9 +149,12 @@ compose_founder_kernel(u64 const * __restrict__ paths_he, u64 const We,
 // The common case is therefore `taken = path word & ~blocked siblings` with no per-edge load. The first version loaded edge_src
 // / edge_tgt for every set bit (~1.9 G scattered 4-byte loads on c4: L2 sector throughput, 520 GB/s of algorithmic traffic);
 // with only first ALTs exempted the ~5 k second-ALT bits per row still cost a dependent-load chain each (750 GB/s).
-// One warp per output row, K2A_UNROLL × 32 words (8192 edges at 4) per step with all loads of a step issued together.
+// One warp per output row, K2A_UNROLL × 32 words (16,384 edges at 8) per step with all loads of a step issued together.
 // Algorithmic bytes: rows × E_pad / 8 read + the same written. Roofline: HBM.
-constexpr int K2A_UNROLL = 4;
+#ifndef V2M_K2A_UNROLL
+#define V2M_K2A_UNROLL 8		// c4: 4 → 2.21 ms, 8 → 1.75 ms, 16 → 1.98 ms (only 34 warps per SM exist: each must keep more bytes in flight)
+#endif
+constexpr int K2A_UNROLL = V2M_K2A_UNROLL;
 
 __global__ void __launch_bounds__(256)
 resolve_rows_kernel(u64 const * __restrict__ lines, u32 const * __restrict__ line_idx, u32 const n_rows, u64 const We,
