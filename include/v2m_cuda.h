@@ -257,6 +257,30 @@ int v2m_cuda_paths_from_genotypes_both(const uint16_t *gt, uint64_t n_records, u
                                        uint64_t h_pad, uint64_t e_pad, void *d_paths_by_edge_and_chrom_copy, void *d_paths_by_chrom_copy_and_edge,
                                        uint64_t *overlaps, uint64_t overlap_cap, uint64_t *n_overlaps);
 
+/* K5 for callers that cannot allocate. No counterpart in the reference: added for code
+ * under CUDA graph capture, tight serving loops and harnesses that forbid cudaMalloc. Same result as
+ * v2m_cuda_paths_from_genotypes_device, but EVERY array is device memory the caller owns (d_gt: n_records * n_copies uint16;
+ * d_alt_offsets: n_records + 1 uint64; d_edges_by_alt; d_record_ref_pos: n_records uint64 and d_edge_target_pos: n_edges
+ * uint64, both only needed with n_overlaps != NULL; d_paths: e_pad * h_pad / 8 bytes, zeroed here; d_overlaps: overlap_cap
+ * (record, row) uint64 pairs, written in NO particular order — sort by (record, row) for the reference's reporting order),
+ * and the call makes no cudaMalloc / cudaFree / stream or event creation: the kernels' scratch (error flags, overlap counter,
+ * 8 bytes of state per chromosome copy) is a static device array of V2M_NO_ALLOC_SCRATCH_BYTES that every GPU which loads
+ * the library holds until the process exits.
+ * LIMIT: n_copies <= V2M_NO_ALLOC_MAX_COPIES, else V2M_ERR_ARGUMENT (use v2m_cuda_paths_from_genotypes_device).
+ * The array is shared by every call on a GPU and keeps the last call's contents (the part a call uses is cleared on `stream`
+ * first): calls that overlap on one GPU — two host threads, or two streams — race; serialise them.
+ * Work is enqueued on `stream` (NULL = the default stream); the call returns after the stream has drained, with
+ * V2M_ERR_ARGUMENT for a genotype naming an ALT its record does not have, or when more than overlap_cap pairs were found
+ * (needed count in *n_overlaps; the first overlap_cap pairs are valid). */
+#define V2M_NO_ALLOC_MAX_COPIES 65536u
+#define V2M_NO_ALLOC_SCRATCH_BYTES (256u + 8u * V2M_NO_ALLOC_MAX_COPIES)   /* 524,544 bytes per GPU */
+int v2m_cuda_ingest_genotypes_no_alloc(const void *d_gt, uint64_t n_records, uint32_t n_copies,
+                                       const void *d_alt_offsets, const void *d_edges_by_alt,
+                                       const void *d_record_ref_pos, const void *d_edge_target_pos, uint64_t n_edges,
+                                       uint64_t h_pad, uint64_t e_pad, void *d_paths,
+                                       void *d_overlaps /* device, [overlap_cap][2] */, uint64_t overlap_cap, uint64_t *n_overlaps,
+                                       void *stream);
+
 /* --- synthetic workloads (measurement infrastructure) ------------------------------------------------ */
 /* Fills d_dst (device, e_pad × h_pad/64 words = paths_by_edge_and_chrom_copy) with LD-structured path bits that are a
  * pure function of (seed, chromosome copy, site); per edge: its site, its 0-based ALT number, the site's ALT count. */

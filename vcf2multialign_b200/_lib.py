@@ -91,6 +91,7 @@ SYMBOLS = {
     "v2m_cuda_paths_from_genotypes": (_i32, [_vp, _u64, _u32, _vp, _vp, _vp, _vp, _u64, _u64, _u64, _vp, _vp, _u64, _vp]),
     "v2m_cuda_paths_from_genotypes_device": (_i32, [_vp, _u64, _u32, _vp, _vp, _vp, _vp, _u64, _u64, _u64, _vp, _vp, _u64, _vp]),
     "v2m_cuda_paths_from_genotypes_both": (_i32, [_vp, _u64, _u32, _vp, _vp, _vp, _vp, _u64, _u64, _u64, _vp, _vp, _vp, _u64, _vp]),
+    "v2m_cuda_ingest_genotypes_no_alloc": (_i32, [_vp, _u64, _u32, _vp, _vp, _vp, _vp, _u64, _u64, _u64, _vp, _vp, _u64, _vp, _vp]),
     "v2m_cuda_time_ingest_genotypes": (_i32, [_vp, _u64, _u32, _vp, _vp, _u64, _u64, _vp, _i32, _vp]),
     "v2m_cuda_synth_paths": (_i32, [_vp, _u64, _u64, _u32, _u64, _u32, _vp, _vp, _vp]),
     "v2m_cuda_time_emit_rows": (_i32, [_vp, _u32, _u32, _vp, _u64, _i32, _vp]),

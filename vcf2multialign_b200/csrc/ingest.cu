@@ -16,8 +16,10 @@
 //   genotype_overlaps_kernel  one thread per chromosome copy walks the records (loads coalesced across copies) and appends
 //                             (record, row) pairs; state (the copy's current target position) is kept between record blocks.
 #include <algorithm>
+#include <atomic>
 #include <cstring>
 #include <limits>
+#include <string>
 #include <thread>
 #include <vector>
 
@@ -526,5 +528,99 @@ extern "C" int v2m_cuda_time_ingest_genotypes(const void *d_gt, uint64_t n_recor
 	cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(d_bad);
 	if (cudaSuccess != err) return fail(V2M_ERR_CUDA, std::string("time_ingest_genotypes: ") + cudaGetErrorString(err));
 	*ms_mean = ms / float(iters);
+	return V2M_OK;
+}
+
+
+// ---- K5 without allocations ---------------------------------------------------------------------------------------------------
+// No counterpart in the reference: added for callers that cannot call cudaMalloc (CUDA
+// graph capture, tight serving loops, harnesses that forbid it). The scratch the two K5 kernels need — the error flags, the
+// overlap counter and the per-chromosome-copy "target of the previous ALT edge" state of genotype_overlaps_kernel — lives in
+// one file-scope device array instead of cudaMalloc'ed buffers. Every GPU that loads the library holds the array until the
+// process exits; every call on a GPU shares it, so calls that overlap on that GPU race (the header says so).
+namespace v2m {
+
+constexpr u64 NO_ALLOC_STATE_OFFSET = 256;			// [0, 4): error flags, [8, 16): overlap count, [256, 256 + 8 * copies): state
+static_assert(V2M_NO_ALLOC_SCRATCH_BYTES == NO_ALLOC_STATE_OFFSET + 8ull * V2M_NO_ALLOC_MAX_COPIES, "scratch layout");
+static __device__ __align__(256) unsigned char k5_no_alloc_scratch[V2M_NO_ALLOC_SCRATCH_BYTES];
+
+namespace {
+	// The array's name is only a stand-in on the host: the device address is asked for once per device, with that device current.
+	int no_alloc_scratch(unsigned char **out)
+	{
+		constexpr int MAX_DEVICES = 64;
+		static std::atomic<unsigned char *> by_device[MAX_DEVICES];
+		int dev(-1);
+		V2M_CUDA_TRY(cudaGetDevice(&dev));
+		if (dev < 0 || dev >= MAX_DEVICES) return fail(V2M_ERR_ARGUMENT, "ingest_genotypes_no_alloc: device index beyond 63");
+		unsigned char *p(by_device[dev].load(std::memory_order_acquire));
+		if (!p)
+		{
+			void *sym(nullptr);
+			cudaError_t const err(cudaGetSymbolAddress(&sym, k5_no_alloc_scratch));
+			if (cudaSuccess != err || !sym)
+				return fail(V2M_ERR_CUDA, std::string("ingest_genotypes_no_alloc: cudaGetSymbolAddress: ") + cudaGetErrorString(err));
+			p = static_cast<unsigned char *>(sym);
+			by_device[dev].store(p, std::memory_order_release);		// two threads racing here store the same address
+		}
+		*out = p;
+		return V2M_OK;
+	}
+}
+
+} // namespace v2m
+
+extern "C" int v2m_cuda_ingest_genotypes_no_alloc(const void *d_gt, uint64_t n_records, uint32_t n_copies,
+	const void *d_alt_offsets, const void *d_edges_by_alt, const void *d_record_ref_pos, const void *d_edge_target_pos, uint64_t n_edges,
+	uint64_t h_pad, uint64_t e_pad, void *d_paths, void *d_overlaps, uint64_t overlap_cap, uint64_t *n_overlaps, void *stream)
+{
+	using namespace v2m;
+	if (!d_paths) return fail(V2M_ERR_ARGUMENT, "ingest_genotypes_no_alloc: NULL output");
+	if (0 != h_pad % 64 || 0 != e_pad % 64 || h_pad < n_copies)
+		return fail(V2M_ERR_ARGUMENT, "ingest_genotypes_no_alloc: path matrix dimensions must be multiples of 64 covering all chromosome copies");
+	if (n_copies > V2M_NO_ALLOC_MAX_COPIES)
+		return fail(V2M_ERR_ARGUMENT, "ingest_genotypes_no_alloc: " + std::to_string(n_copies) + " chromosome copies exceed the static scratch (V2M_NO_ALLOC_MAX_COPIES = "
+			+ std::to_string(V2M_NO_ALLOC_MAX_COPIES) + "); use v2m_cuda_paths_from_genotypes_device");
+	if (h_pad / 32 > 0xffffffffull) return fail(V2M_ERR_ARGUMENT, "ingest_genotypes_no_alloc: h_pad too large");
+	if (n_records && n_copies && (!d_gt || !d_alt_offsets || !d_edges_by_alt)) return fail(V2M_ERR_ARGUMENT, "ingest_genotypes_no_alloc: NULL argument");
+	bool const want_overlaps(nullptr != n_overlaps);
+	if (want_overlaps && (!d_record_ref_pos || !d_edge_target_pos)) return fail(V2M_ERR_ARGUMENT, "ingest_genotypes_no_alloc: overlaps need record_ref_pos and edge_target_pos");
+	if (want_overlaps && overlap_cap && !d_overlaps) return fail(V2M_ERR_ARGUMENT, "ingest_genotypes_no_alloc: NULL overlap buffer");
+
+	cudaStream_t const st(static_cast<cudaStream_t>(stream));
+	unsigned char *scratch(nullptr);
+	if (int const rc = no_alloc_scratch(&scratch)) return rc;
+	u32 *const d_bad(reinterpret_cast<u32 *>(scratch));
+	unsigned long long *const d_count(reinterpret_cast<unsigned long long *>(scratch + 8));
+	u64 *const d_state(reinterpret_cast<u64 *>(scratch + NO_ALLOC_STATE_OFFSET));
+
+	// The array keeps the last call's contents: flags, counter and the state of the copies of this call start at zero.
+	V2M_CUDA_TRY(cudaMemsetAsync(scratch, 0, NO_ALLOC_STATE_OFFSET + 8ull * n_copies, st));
+	if (e_pad && h_pad) V2M_CUDA_TRY(cudaMemsetAsync(d_paths, 0, e_pad * h_pad / 8, st));
+	if (n_records && n_copies)
+	{
+		launch_ingest(static_cast<unsigned short const *>(d_gt), n_records, n_copies, static_cast<u64 const *>(d_alt_offsets), static_cast<u64 const *>(d_edges_by_alt),
+			u32(h_pad / 32), e_pad, static_cast<u32 *>(d_paths), d_bad, st);
+		V2M_CHECK_LAUNCH("ingest_genotypes_kernel (no_alloc)");
+		if (want_overlaps)
+		{
+			genotype_overlaps_kernel<<<(n_copies + 127) / 128, 128, 0, st>>>(static_cast<unsigned short const *>(d_gt), n_records, 0, n_copies,
+				static_cast<u64 const *>(d_alt_offsets), static_cast<u64 const *>(d_edges_by_alt), static_cast<u64 const *>(d_record_ref_pos),
+				static_cast<u64 const *>(d_edge_target_pos), n_edges, d_state, static_cast<u64 *>(d_overlaps), overlap_cap, d_count);
+			V2M_CHECK_LAUNCH("genotype_overlaps_kernel (no_alloc)");
+		}
+	}
+	// Flags and counter come back through a 16-byte copy into this frame; the call returns when the stream has drained.
+	u64 head[2] = {0, 0};
+	V2M_CUDA_TRY(cudaMemcpyAsync(head, scratch, 16, cudaMemcpyDeviceToHost, st));
+	V2M_CUDA_TRY(cudaStreamSynchronize(st));
+	u32 const bad{static_cast<u32>(head[0])};
+	if (bad & 1u) return fail(V2M_ERR_ARGUMENT, "ingest_genotypes_no_alloc: a genotype refers to an ALT its record does not have (the reference asserts, variant_graph.cc:399)");
+	if (bad & 2u) return fail(V2M_ERR_ARGUMENT, "ingest_genotypes_no_alloc: edge index beyond e_pad");
+	if (want_overlaps)
+	{
+		*n_overlaps = head[1];
+		if (head[1] > overlap_cap) return fail(V2M_ERR_ARGUMENT, "ingest_genotypes_no_alloc: overlap capacity too small (needed count is in *n_overlaps)");
+	}
 	return V2M_OK;
 }
