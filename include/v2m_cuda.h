@@ -189,10 +189,12 @@ int v2m_cuda_stream_rows(v2m_plan_t p, int unaligned, v2m_row_sink sink, void *s
  *   joined triples (lhs_rep, rhs_rep, size) in permutation order: joined_offsets[c-1] … joined_offsets[c] index into joined
  *   (for c = 1 the lhs is V2M_PLOIDY_MAX: the single-segment case of :474-509). joined holds joined_cap triples; if that is
  *   too small the call returns V2M_ERR_ARGUMENT with the needed count in joined_offsets[n_cuts-1].
- * LIMIT: at most 8192 chromosome copies — the sweep keeps the pBWT state (permutation as 16-bit positions, divergence) of all
- * copies in one CTA's shared memory; the reference's pbwt_context (include/vcf2multialign/pbwt.hh:61-74) has no such limit.
- * 1000 Genomes phase 3 (5,008 copies) fits; 1000G + HGDP (~8,400) or larger cohorts do not and get V2M_ERR_ARGUMENT from the
- * three founder-mode calls (K3, find_matchings, find_cut_positions). Row emission has no such limit. */
+ * LIMIT: at most 16,384 chromosome copies — the sweep keeps the pBWT state (permutation as 16-bit positions, divergence) of
+ * all copies in one CTA's shared memory (10 bytes per copy + two column buffers: 225 of the 227 KiB a CTA may have at
+ * 16,384 copies); the reference's pbwt_context (include/vcf2multialign/pbwt.hh:61-74) has no such limit. 1000 Genomes phase 3
+ * (5,008 copies) and 1000G + HGDP (~8,400) fit; above 8,192 copies the kernels spill a few registers and run slower per
+ * column. Larger cohorts get V2M_ERR_ARGUMENT from the three founder-mode calls (K3, find_matchings, find_cut_positions).
+ * Row emission has no such limit. */
 int v2m_cuda_segment_classes(v2m_graph_t g, const uint64_t *cut_positions, uint64_t n_cuts,
                              uint32_t *rhs_eq, uint32_t *distinct, uint32_t *first_class, uint8_t *first_is_ref,
                              uint64_t *joined_offsets /* [n_cuts] */, uint32_t *joined, uint64_t joined_cap);
@@ -213,7 +215,7 @@ int v2m_cuda_find_matchings(v2m_graph_t g, const uint64_t *cut_positions, uint64
  * host. cut_positions receives *n_cuts node ids (first 0, last the sink, as cut_positions() returns them); *score =
  * max_segmentation_height() (the CLI prints 1 + score, main.cc:520); *found = what the reference's member returns (0 iff
  * the score is CUT_POSITION_SCORE_MAX). If cap is too small the call returns V2M_ERR_ARGUMENT with the needed count in
- * *n_cuts. At most 8192 chromosome copies. */
+ * *n_cuts. At most 16,384 chromosome copies (see v2m_cuda_segment_classes). */
 int v2m_cuda_find_cut_positions(v2m_graph_t g, uint64_t min_distance, uint64_t *cut_positions, uint64_t cap,
                                 uint64_t *n_cuts, uint32_t *score, int *found);
 /* Timing of the calling thread's last v2m_cuda_find_cut_positions: ms4 = {local sweep, boundary composition, list extraction

@@ -514,9 +514,10 @@ def test_segment_classes_random_graphs(v2m, tmp_path, chunks, monkeypatch):
     assert done == 12
 
 
-@pytest.mark.parametrize("n_samples,chunks", [(520, "4"), (1100, "6"), (2504, None)])
+@pytest.mark.parametrize("n_samples,chunks", [(520, "4"), (1100, "6"), (2504, None), (4300, "5"), (5500, None), (8192, None), (8192, "3")])
 def test_segment_classes_many_copies(v2m, n_samples, chunks, monkeypatch):
-    """More chromosome copies than one warp-word per warp (KW 2, 3 and the 5,008-copy shape of c3), LD-structured bits."""
+    """More chromosome copies than one warp-word per warp (KW 2, 3 and the 5,008-copy shape of c3), LD-structured bits; beyond
+    8,192 copies (1000 Genomes + HGDP has ~8,400) up to the 16,384 the sweep holds: KW 10, 12 and 16."""
     from vcf2multialign_b200 import synth
     if chunks is None:
         monkeypatch.delenv("V2M_K3_CHUNKS", raising=False)
@@ -627,9 +628,9 @@ def test_cut_positions_random_graphs(v2m, tmp_path, chunks, cap, monkeypatch):
             _check_cuts(og, dg, md, f"seed {seed} md {md} chunks {chunks} cap {cap}")
 
 
-@pytest.mark.parametrize("n_samples,chunks,cap", [(520, "4", None), (1100, "7", "4"), (2504, None, None)])
+@pytest.mark.parametrize("n_samples,chunks,cap", [(520, "4", None), (1100, "7", "4"), (2504, None, None), (4300, None, None), (6900, "7", "4"), (8192, None, None)])
 def test_cut_positions_many_copies(v2m, n_samples, chunks, cap, monkeypatch):
-    """KW 2, 3 and the 5,008-copy shape of c3 on LD-structured bits; then find_matchings on the device-made cuts."""
+    """KW 2, 3 and the 5,008-copy shape of c3 on LD-structured bits, and 8,600 / 13,800 / 16,384 copies (KW 10, 14, 16)."""
     from vcf2multialign_b200 import synth
     for name, val in (("V2M_K3_CHUNKS", chunks), ("V2M_K4_CAP", cap)):
         if val is None:
@@ -647,6 +648,20 @@ def test_cut_positions_many_copies(v2m, n_samples, chunks, cap, monkeypatch):
     for md in (0, 50, 1000):
         cuts = _check_cuts(og, dg, md, f"synth {n_samples} md {md}")
         assert cuts is not None
+
+
+def test_founder_mode_refuses_more_than_16384_copies(v2m):
+    """The sweep keeps the state of all copies in one CTA's shared memory: 16,386 copies are refused with a clear message (row
+    emission on the same graph is unaffected)."""
+    from vcf2multialign_b200 import synth
+    w = synth.make_workload("custom", seed=7, ref_len=20_000, n_sites=300, n_samples=8193, with_paths=True)
+    dg = v2m.DeviceGraph(w.graph, w.ref)
+    with pytest.raises(v2m.V2MError, match="16384"):
+        dg.find_cut_positions(0)
+    with pytest.raises(v2m.V2MError, match="16384"):
+        dg.segment_classes(np.array([0, 5, 9], np.uint64))
+    rows = dg.plan_haplotypes([0, 16385]).emit_rows()
+    assert rows.shape[0] == 2
 
 
 def test_cut_positions_degenerate(v2m, tmp_path):

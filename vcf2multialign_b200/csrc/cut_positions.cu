@@ -99,7 +99,7 @@ __device__ __forceinline__ void k4_candidate(k4_params const &P, k3_smem const &
 		n_top += top ? 1u : 0u;
 		n_young += young ? 1u : 0u;
 	}
-	u32 const tot(k4_block_add(n_top | (n_young << 16), ex));				// H <= 8192: both halves fit 16 bits
+	u32 const tot(k4_block_add(n_top | (n_young << 16), ex));				// H <= 16,384: both halves fit 16 bits
 	u32 const top_total(tot & 0xffffu), young_total(tot >> 16);
 
 	// Bins → pairs: thread t owns age t, i.e. index cur - t; descending index = ascending age.
@@ -215,7 +215,7 @@ k4_pack_lists_kernel(u32 const *__restrict__ list_q, u32 const *__restrict__ lis
 		for (u32 i(lane); i < n; i += 32)
 		{
 			out_q[dst + i] = list_q[src + i];
-			out_eq[dst + i] = (unsigned short) list_eq[src + i];		// eq < cap <= H + 1 <= 8193
+			out_eq[dst + i] = (unsigned short) list_eq[src + i];		// eq < cap <= H + 1 <= 16,385
 		}
 	}
 }
@@ -247,7 +247,8 @@ namespace {
 		{
 			V2M_K4_CASE(1); V2M_K4_CASE(2); V2M_K4_CASE(3); V2M_K4_CASE(4);
 			V2M_K4_CASE(5); V2M_K4_CASE(6); V2M_K4_CASE(7); V2M_K4_CASE(8);
-			default: return fail(V2M_ERR_ARGUMENT, "find_cut_positions: more than 8192 chromosome copies are not supported yet");
+			V2M_K4_CASE(10); V2M_K4_CASE(12); V2M_K4_CASE(14); V2M_K4_CASE(16);
+			default: return fail(V2M_ERR_ARGUMENT, "find_cut_positions: more than 16384 chromosome copies are not supported");
 		}
 #undef V2M_K4_CASE
 	}
@@ -269,9 +270,8 @@ int find_cut_positions_host(graph_holder const &gh, u64 const min_distance, std:
 	out_cut_positions.clear();
 	out_score = CUT_POSITION_SCORE_MAX;
 	if (0 == g.H) return fail(V2M_ERR_ARGUMENT, "find_cut_positions: no chromosome copies (the reference reads an empty divergence map, find_cut_positions.cc:137)");
-	u32 const words((g.H + 31) / 32);
-	u32 const KW((words + K3_WARPS - 1) / K3_WARPS);
-	if (KW > K3_KW_MAX) return fail(V2M_ERR_ARGUMENT, "find_cut_positions: more than 8192 chromosome copies are not supported yet");
+	u32 const KW(k3_words_per_warp(g.H));
+	if (0 == KW) return fail(V2M_ERR_ARGUMENT, "find_cut_positions: more than 16384 chromosome copies are not supported");
 	u32 const Hp(KW * K3_WARPS * 32);
 	if (g.E >= 0xfffffff0u) return fail(V2M_ERR_ARGUMENT, "find_cut_positions: edge indices do not fit 32 bits");
 	auto const t_begin(std::chrono::steady_clock::now());
@@ -329,6 +329,7 @@ int find_cut_positions_host(graph_holder const &gh, u64 const min_distance, std:
 		V2M_CUDA_TRY(cudaGetDevice(&dev));
 		V2M_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
 		u32 const smem(k3_smem_bytes(Hp, u32(g.Wh)));
+		if (int const rc = k3_check_smem(smem, "find_cut_positions")) return rc;
 		u64 P(sms);
 		if (char const *env = std::getenv("V2M_K3_CHUNKS"))		// tests force small / odd chunk counts
 			if (int const v = std::atoi(env); v > 0) P = u64(v);

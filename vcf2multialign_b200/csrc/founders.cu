@@ -22,7 +22,7 @@
 //   pass C  k3_emit_kernel      P CTAs. Chunk j repeats its sweep from the true state and, at every cut it owns, derives the
 //                               class representatives, the distinct count, permutation.front(), rhs_first_path_is_ref and the
 //                               joined (lhs_rep, rhs_rep, size) runs in permutation order.
-// One column step is a CTA-wide stable partition of H <= 8192 positions kept in shared memory (permutation u16,
+// One column step is a CTA-wide stable partition of H <= 16,384 positions kept in shared memory (permutation u16,
 // divergence u32): ballots give the zero/one masks, the divergence maxima "since the previous zero / one" are two
 // warp-segmented max-scans (skipped for words that are all zeros or all ones, the common case for rare alleles), one
 // cross-warp exchange through shared memory, then an in-place scatter. Columns arrive through bulk async copies
@@ -237,7 +237,11 @@ namespace {
 			case 6: return k3_launch<6>(pass, P, n_ctas, smem, stream);
 			case 7: return k3_launch<7>(pass, P, n_ctas, smem, stream);
 			case 8: return k3_launch<8>(pass, P, n_ctas, smem, stream);
-			default: return fail(V2M_ERR_ARGUMENT, "segment_classes: more than 8192 chromosome copies are not supported yet");
+			case 10: return k3_launch<10>(pass, P, n_ctas, smem, stream);
+			case 12: return k3_launch<12>(pass, P, n_ctas, smem, stream);
+			case 14: return k3_launch<14>(pass, P, n_ctas, smem, stream);
+			case 16: return k3_launch<16>(pass, P, n_ctas, smem, stream);
+			default: return fail(V2M_ERR_ARGUMENT, "segment_classes: more than 16384 chromosome copies are not supported");
 		}
 	}
 }
@@ -254,9 +258,8 @@ int segment_classes_host(graph_holder const &gh, u64 const *cut_positions, u64 c
 	if (!cut_positions || n_cuts < 1) return fail(V2M_ERR_ARGUMENT, "segment_classes: no cut positions");
 	if (0 != cut_positions[0]) return fail(V2M_ERR_ARGUMENT, "segment_classes: first cut position must be node 0 (founder_sequence_greedy_output.cc:168)");
 	if (0 == g.H) return fail(V2M_ERR_ARGUMENT, "segment_classes: no chromosome copies");
-	u32 const words((g.H + 31) / 32);
-	u32 const KW((words + K3_WARPS - 1) / K3_WARPS);
-	if (KW > K3_KW_MAX) return fail(V2M_ERR_ARGUMENT, "segment_classes: more than 8192 chromosome copies are not supported yet");
+	u32 const KW(k3_words_per_warp(g.H));
+	if (0 == KW) return fail(V2M_ERR_ARGUMENT, "segment_classes: more than 16384 chromosome copies are not supported");
 	u32 const Hp(KW * K3_WARPS * 32);
 	u64 const n_seg(n_cuts - 1);
 
@@ -281,6 +284,7 @@ int segment_classes_host(graph_holder const &gh, u64 const *cut_positions, u64 c
 	V2M_CUDA_TRY(cudaGetDevice(&dev));
 	V2M_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
 	u32 const smem(k3_smem_bytes(Hp, u32(g.Wh)));
+	if (int const rc = k3_check_smem(smem, "segment_classes")) return rc;
 	u64 P(max_chunks > 0 ? u64(max_chunks) : u64(sms));
 	if (char const *env = (max_chunks > 0 ? nullptr : std::getenv("V2M_K3_CHUNKS")))		// tests force small / odd chunk counts
 		if (int const v = std::atoi(env); v > 0) P = u64(v);

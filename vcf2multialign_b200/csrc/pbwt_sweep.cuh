@@ -16,7 +16,8 @@ namespace v2m {
 
 constexpr int K3_THREADS = 1024;
 constexpr int K3_WARPS = K3_THREADS / 32;
-constexpr int K3_KW_MAX = 8;					// 32-position words per warp → H <= 32 · 8 · 32 = 8192
+constexpr int K3_KW_MAX = 16;					// 32-position words per warp → H <= 32 · 16 · 32 = 16,384
+constexpr int K3_KW_REGS = 8;					// up to here a thread keeps (position, divergence, zero mask) per word in registers
 constexpr int K3_COLB = 16;						// columns per bulk copy
 constexpr u32 K3_SENT = 0xffffffffu;			// "differs on an artificial column" marker of pass B
 constexpr unsigned FULL = 0xffffffffu;
@@ -59,7 +60,11 @@ __device__ __forceinline__ u32 pbwt_step(k3_state const &st, u32 const first_val
 	u32 const base(warp * KW * 32);
 	u32 const below(lanes_below(lane));
 
-	u32 p[KW], nd[KW], zm[KW];
+	// KW > K3_KW_REGS (more than 8,192 chromosome copies): 3 · KW registers per thread do not fit the 64 a 1,024-thread CTA
+	// leaves, so the positions are kept as 16-bit pairs and the zero masks are ballotted again in the second half (bit_of reads
+	// the staged column or the class ids, neither changes during the step).
+	constexpr bool lean(KW > K3_KW_REGS);
+	u32 p[lean ? (KW + 1) / 2 : KW], nd[KW], zm[lean ? 1 : KW];
 	u32 open(0);							// bit k: this lane's window reaches back beyond the warp's range
 	u32 cz(0), co(0), zc(0);
 	bool seen_z(false), seen_o(false);
@@ -109,7 +114,9 @@ __device__ __forceinline__ u32 pbwt_step(k3_state const &st, u32 const first_val
 			co = (O >> 31) ? 0 : vo31;
 			seen_z = true; seen_o = true;
 		}
-		p[k] = pk; nd[k] = v; zm[k] = Z;
+		nd[k] = v;
+		if constexpr (lean) p[k / 2] = (k & 1) ? (p[k / 2] | (pk << 16)) : pk;
+		else { p[k] = pk; zm[k] = Z; }
 		zc += __popc(Z);
 	}
 
@@ -139,13 +146,19 @@ __device__ __forceinline__ u32 pbwt_step(k3_state const &st, u32 const first_val
 	for (int k = 0; k < KW; ++k)
 	{
 		u32 const i(base + k * 32 + lane);
-		u32 const Z(zm[k]);
+		u32 pk, Z;
+		if constexpr (lean)
+		{
+			pk = (p[k / 2] >> (16 * (k & 1))) & 0xffffu;
+			Z = ~__ballot_sync(FULL, pk >= st.H ? true : bit_of(pk));
+		}
+		else { pk = p[k]; Z = zm[k]; }
 		bool const bit(0 == (Z >> lane & 1));
 		u32 const zb(zp + __popc(Z & below));
 		u32 const np(bit ? ztotal + (i - zb) : zb);
 		u32 dv(nd[k]);
 		if (open >> k & 1) dv = max(dv, bit ? cin_o : cin_z);
-		st.perm[np] = (unsigned short) p[k];
+		st.perm[np] = (unsigned short) pk;
 		st.div[np] = dv;
 		zp += __popc(Z);
 	}
@@ -444,6 +457,28 @@ inline int k3_launch_ab(int const pass, k3_params const &P, u32 const n_ctas, u3
 		k3_compose_kernel<KW><<<1, K3_THREADS, smem, stream>>>(P);
 		V2M_CHECK_LAUNCH("k3_compose_kernel");
 	}
+	return 0;
+}
+
+// 32-position words per warp for H chromosome copies: exact up to K3_KW_REGS, the next even count above (fewer instantiations;
+// positions beyond H are padding that always sorts last). 0: more than 32 · K3_KW_MAX · 32 copies.
+inline u32 k3_words_per_warp(u32 const H)
+{
+	u32 const words((H + 31) / 32);
+	u32 KW(std::max<u32>(1, (words + K3_WARPS - 1) / K3_WARPS));
+	if (KW > u32(K3_KW_REGS)) KW = (KW + 1) & ~1u;
+	return KW <= u32(K3_KW_MAX) ? KW : 0;
+}
+
+// The sweep's shared memory against what a CTA may have on this device.
+inline int k3_check_smem(u32 const smem, char const *who)
+{
+	int dev(0), limit(0);
+	V2M_CUDA_TRY(cudaGetDevice(&dev));
+	V2M_CUDA_TRY(cudaDeviceGetAttribute(&limit, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
+	if (smem > u32(limit))
+		return fail(V2M_ERR_ARGUMENT, std::string(who) + ": the pBWT state of this many chromosome copies needs " + std::to_string(smem)
+			+ " bytes of shared memory, the device gives a CTA " + std::to_string(limit));
 	return 0;
 }
 
