@@ -497,18 +497,32 @@ int v2m_cuda_plan_founders(v2m_graph_t g, const uint64_t *cut_positions, uint64_
 	// The last segment runs to the end of the edge list whatever the final cut node is.
 	cut_edges[n_segments] = g->g.E;
 
+	bool const trace(nullptr != std::getenv("V2M_TRACE"));		// host-side phase times on stderr
+	auto mark([&, t_last = std::chrono::steady_clock::now()](char const *what) mutable {
+		if (!trace) return;
+		cudaDeviceSynchronize();
+		auto const now(std::chrono::steady_clock::now());
+		std::fprintf(stderr, "[plan_founders] %-32s %8.2f ms\n", what, std::chrono::duration<double, std::milli>(now - t_last).count());
+		t_last = now;
+	});
 	auto holder(std::make_unique<v2m_plan_s>());
 	holder->owner = g;
 	holder->p.graph = &g->g;
 	holder->p.n_rows = n_founders;
 	if (int const st = dev_alloc(holder->p.taken, u64(n_founders) * g->g.We)) return st;
+	mark("cut edges + taken buffer");
 	u64 *d_cut_edges(nullptr), *d_lines(nullptr);
 	u32 *d_assigned(nullptr), *d_bad(nullptr);
 	int st(V2M_OK);
 	do
 	{
 		if ((st = dev_upload(d_cut_edges, cut_edges.data(), cut_edges.size()))) break;
+		// `assigned` is 54 MB on c3 and lives in pageable memory: this copy (4 – 6 ms) is most of the call. Sending it through the
+		// pinned staging pair in 8 MiB pieces measured the same 3.9 – 6.2 ms (the host-side copy into the pinned pieces is the
+		// bound) and cost 60 ms on a process's first call, so it stays a plain copy; callers that keep `assigned` in memory
+		// from v2m_cuda_host_alloc get link speed (~1 ms).
 		if ((st = dev_upload(d_assigned, assigned, n_segments * n_founders))) break;
+		mark("assigned upload");
 		if ((st = dev_alloc(d_lines, u64(n_founders) * g->g.We))) break;
 		// the range check of `assigned` runs on the device (13.5 M entries on c3: a host loop cost more than the whole plan)
 		if ((st = dev_alloc(d_bad, 1))) break;
@@ -520,6 +534,7 @@ int v2m_cuda_plan_founders(v2m_graph_t g, const uint64_t *cut_positions, uint64_
 		cudaError_t const err(cudaMemcpy(&bad, d_bad, sizeof(u32), cudaMemcpyDeviceToHost));		// synchronises with the default stream
 		if (cudaSuccess != err) st = fail(V2M_ERR_CUDA, std::string("plan_founders: ") + cudaGetErrorString(err));
 		else if (bad) st = fail(V2M_ERR_ARGUMENT, "plan_founders: assigned chromosome copy out of range");
+		mark("check + compose + resolve");
 	} while (false);
 	cudaFree(d_cut_edges); cudaFree(d_assigned); cudaFree(d_bad);
 	if (st) { cudaFree(d_lines); return st; }

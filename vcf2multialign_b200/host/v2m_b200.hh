@@ -591,19 +591,23 @@ private:
 	{
 		// A founder column assigned PLOIDY_MAX in every segment follows REF edges only: that is the REF row (:519-531).
 		std::uint64_t const segments(m_assigned_samples.rows);
-		std::vector<std::uint32_t> assigned;
+		// The matrix is 54 MB on config 3: it is only copied when the REF column has to be put in front of it.
+		std::vector<std::uint32_t> with_ref;
+		std::uint32_t const *assigned(m_assigned_samples.data.data());
 		std::uint32_t n_rows(0);
 		if (this->m_should_output_reference)
 		{
-			assigned.assign(segments, V2M_PLOIDY_MAX);
+			with_ref.reserve(segments * (1 + m_assigned_samples.cols));
+			with_ref.assign(segments, V2M_PLOIDY_MAX);
+			with_ref.insert(with_ref.end(), m_assigned_samples.data.begin(), m_assigned_samples.data.end());
+			assigned = with_ref.data();
 			rows.push_back({this->a2m_id("REF"), "REF"});
 			++n_rows;
 		}
-		assigned.insert(assigned.end(), m_assigned_samples.data.begin(), m_assigned_samples.data.end());
 		for (std::uint32_t f(0); f < m_assigned_samples.cols; ++f, ++n_rows)
 			rows.push_back({this->a2m_id(std::to_string(1 + f)), std::to_string(1 + f)});								// :539-542
 		v2m_plan_t p{};
-		check(v2m_cuda_plan_founders(dg.get(), m_cut_positions.data(), segments, assigned.data(), n_rows, &p));
+		check(v2m_cuda_plan_founders(dg.get(), m_cut_positions.data(), segments, assigned, n_rows, &p));
 		return device_plan(p);
 	}
 
