@@ -30,8 +30,19 @@
 //           destination line starts in the middle of a sector, its 64-byte runs touch three sectors instead of two, and the
 //           kernel reaches 72 % of the copy peak; with C = 6,000,128 (or the c2 shape, or 12,000,000) it reaches 83 %
 //           (scripts/bench_transpose.py --cols …). The layout is the reference's, so the lines cannot be padded.
+//   round 2 what bounds it (profiles/r02_k1_ablation.txt, r02_k1_variants.txt, r02_k1_wide_ncu_summary.txt): nothing is saturated —
+//           DRAM 57 % active, L2 41 – 47 %, ALU pipe 51 %, issue slots 42 %. The transposes alone are issue-bound at 0.72 ms on c5
+//           (~850 instructions per sub-tile, a third of them addresses and predicates), loads hide under them (0.87 ms together)
+//           but stores do not (1.41 ms; 0.96 on a sector-aligned shape), and loads and stores together cost more than the sum of
+//           what each adds alone. Tried on top of the kernels below, none faster on c5: half-size tiles at 4 CTAs per SM (1.62 ms),
+//           a persistent kernel with cp.async prefetch (1.65), two sub-tiles per thread with 8-byte stores in 256-byte runs (the
+//           wide kernel, 1.64; 2.86 when held to 3 CTAs per SM — the L1 that is left no longer covers the loads), ld.global.cg /
+//           L1::no_allocate / .lu / L2 evict-first loads (1.62 / 1.94 / 1.92 / 1.92). The wide kernel wins where destination lines
+//           are 8 mod 16 bytes long and is the launcher's choice there.
 //
 // Algorithmic bytes: 2 · R · C / 8 (each bit read once, written once). Roofline: HBM read + write.
+#include <algorithm>
+#include <atomic>
 #include <cstdlib>
 
 #include "common.cuh"
@@ -155,6 +166,7 @@ transpose_bits_kernel(u64 const * __restrict__ src, u32 * __restrict__ dst, u64 
 constexpr int K1T_TC = 1024;
 constexpr int K1T_TW = 16;
 
+template <int MODE>
 __global__ void __launch_bounds__(K1_THREADS, 2)
 transpose_bits_tall_kernel(u64 const * __restrict__ src, u32 * __restrict__ dst, u64 const R64, u64 const C, u64 const dst_pitch32)
 {
@@ -173,7 +185,7 @@ transpose_bits_tall_kernel(u64 const * __restrict__ src, u32 * __restrict__ dst,
 		for (int p = 0; p < K1T_TC / 64; ++p)
 		{
 			u64 const line(c0 + 64 * p + l_in_pass);
-			vals[p] = (pair_ok && line < C) ? k1_load(src + line * R64 + p0 + q, ld_policy) : 0;
+			vals[p] = (MODE & 2) ? u64(tid) * 0x9e3779b97f4a7c15ull + p : (pair_ok && line < C) ? k1_load(src + line * R64 + p0 + q, ld_policy) : 0;
 		}
 #pragma unroll
 		for (int p = 0; p < K1T_TC / 64; ++p)
@@ -205,7 +217,7 @@ transpose_bits_tall_kernel(u64 const * __restrict__ src, u32 * __restrict__ dst,
 		u32 *out(dst + r0 * dst_pitch32 + xw);
 #pragma unroll
 		for (int j = 0; j < 32; ++j)
-			k1_store(out + u64(j) * dst_pitch32, a[j], st_policy);
+			if (!(MODE & 1) || 0x12345678u == a[j]) k1_store(out + u64(j) * dst_pitch32, a[j], st_policy);
 	}
 }
 
@@ -375,6 +387,275 @@ transpose_bits_sheared_kernel(u64 const * __restrict__ src, u8 * __restrict__ ds
 
 
 
+// Half-size tiles: 512 source lines × 512 rows (64-byte source pieces), 256 threads, 4 CTAs per SM — the same lanes ↔ sub-tiles
+// map and the same 64-byte store runs as transpose_bits_kernel, but four CTAs in four different phases (load / transpose /
+// store) per SM instead of two. Shared layout in 32-bit words: word c of line l at l · 16 + 16 · (l >> 5) + (((c >> 1) ^ ((l >> 6)
+// & 7)) << 1 | (c & 1)): the transposing read of a warp (16 line groups × 2 word columns) hits 32 distinct banks.
+constexpr int K1S_TC = 512;
+constexpr int K1S_TW = 16;
+constexpr int K1S_THREADS = 256;
+constexpr int K1S_SMEM = (K1S_TC * K1S_TW + 16 * (K1S_TC / 32)) * 4;
+
+// MODE (ablations for profiles/r02_k1_ablation.txt, V2M_K1_MODE): 0 the kernel; 1 no stores (kept alive by a test that never
+// holds); 2 no loads (the tile is made of thread indices); 3 neither.
+template <bool EDGE, int MODE = 0>
+__device__ __forceinline__ void k1s_tile(u64 const * __restrict__ src, u32 * __restrict__ dst, u64 const R64, u64 const C, u64 const dst_pitch32, u64 *tile)
+{
+	u64 const c0(u64(blockIdx.y) * K1S_TC);
+	u64 const p0(u64(blockIdx.x) * (K1S_TW / 2));
+	unsigned const tid(threadIdx.x);
+	[[maybe_unused]] u64 const st_policy(1 == V2M_K1_STORE_POLICY ? k1_policy_evict_last() : 0);
+	{
+		unsigned const q(tid & 7), lp(tid >> 3);				// 32 lines per pass
+		u64 const *first(src + (c0 + lp) * R64 + p0 + q);
+		u64 const stride(32 * R64);
+		[[maybe_unused]] bool const pair_ok(p0 + q < R64);
+		u64 vals[K1S_TC / 32];
+#pragma unroll
+		for (int p = 0; p < K1S_TC / 32; ++p)
+			vals[p] = (MODE & 2) ? u64(tid) * 0x9e3779b97f4a7c15ull + p : (!EDGE || (pair_ok && c0 + 32 * p + lp < C)) ? __ldg(first + u64(p) * stride) : 0;
+#pragma unroll
+		for (int p = 0; p < K1S_TC / 32; ++p)
+			tile[(32 * p + lp) * 8 + 8 * p + (q ^ ((p >> 1) & 7))] = vals[p];
+	}
+	__syncthreads();
+
+	unsigned const lane(tid & 31), warp(tid >> 5);
+	unsigned const xl(lane & 15), yl(lane >> 4);
+	unsigned const yw(2 * warp + yl);
+	u32 const *tile32(reinterpret_cast<u32 const *>(tile));
+	u32 a[32];
+	{
+		unsigned const base((32 * xl) * 16 + 16 * xl + (((warp ^ (xl >> 1)) << 1) | yl));
+#pragma unroll
+		for (int i = 0; i < 32; ++i) a[i] = tile32[base + 16 * i];
+	}
+	transpose32(a);
+
+	u64 const xw(c0 / 32 + xl);
+	u64 const r0(64 * p0 + 32 * yw);
+	if (!EDGE || (xw < C / 32 && r0 < 64 * R64))
+	{
+		u32 *out(dst + r0 * dst_pitch32 + xw);
+#pragma unroll
+		for (int j = 0; j < 32; ++j)
+			if (!(MODE & 1) || 0x12345678u == a[j]) k1_store(out + u64(j) * dst_pitch32, a[j], st_policy);
+	}
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(K1S_THREADS, 4)
+transpose_bits_small_kernel(u64 const * __restrict__ src, u32 * __restrict__ dst, u64 const R64, u64 const C, u64 const dst_pitch32)
+{
+	extern __shared__ __align__(16) u64 tile[];
+	bool const edge((u64(blockIdx.y) + 1) * K1S_TC > C || (u64(blockIdx.x) + 1) * (K1S_TW / 2) > R64);
+	if (edge) k1s_tile<true, MODE>(src, dst, R64, C, dst_pitch32, tile);
+	else k1s_tile<false, MODE>(src, dst, R64, C, dst_pitch32, tile);
+}
+
+
+// The tall tile as a stream (opt-in, V2M_K1_TALL=8; the record of an experiment): persistent CTAs, two per SM, draw tiles from
+// a counter, row bands fastest, and the source pieces of the next tile are on their way into shared memory (8-byte cp.async: no
+// registers, no waiting warps) while the current one is transposed and stored. One buffer is enough: the copies are issued
+// right after every thread has read its sub-tiles into registers. 256 threads; every thread takes the two sub-tiles that share
+// its 32 source lines and lie in the word columns 2 w and 2 w + 1 (w = warp): one LDS.64 per source line feeds both, so the
+// swizzle can stay at 64-bit granularity. Stores as in the tall kernel: 128 bytes of one destination line per warp instruction.
+// Why it was tried — the ablations (profiles/r02_k1_ablation.txt, c5): the transposes alone take 0.72 ms (issue-bound, IPC 3.7 of
+// 4), loads + transposes 0.87, transposes + stores 1.41 (tile kernel's store shape; 1.10 with the tall kernel's), everything 1.60
+// – 1.65: the load phase of a CTA stretches when stores are in flight, and with two (or four: the half-size-tile kernel, same
+// time) CTAs per SM nothing covers it.
+// What came out: (1) tiles must be handed out by a counter — with a fixed stride the CTAs that run ahead spread the front of
+// partially written sectors over more of the destination than the L2 holds (stores alone: 2.17 ms on c5, 1.15 – 1.20 with the
+// counter, 0.85 on a sector-aligned shape either way); (2) cp.async in 4- or 8-byte pieces is itself slow — loads + transposes
+// 1.37 ms (4-byte) and 1.25 ms (8-byte) against 0.87 for LDG.64 + STS — so the kernel ends at 1.65 ms on c5, 1.89 on c4, 1.54
+// aligned: no better than the kernels it was meant to beat. 16-byte cp.async and bulk copies need 16-byte aligned source lines,
+// which the layout does not give (R / 8 bytes per line, 8 mod 16 for 5,056 rows).
+// Shared layout in 64-bit words: word q of line l at l · 8 + 8 · (l >> 8) + (q ^ ((l >> 5) & 7)): a half-warp's LDS.64 (lines
+// 32 · lane + i, one q) covers 16 distinct bank pairs.
+constexpr int K1P_THREADS = 256;
+constexpr int K1P_SMEM = (K1T_TC * 8 + 8 * (K1T_TC / 256)) * 8;
+
+template <int MODE>
+__global__ void __launch_bounds__(K1P_THREADS, 2)
+transpose_bits_tall_pairs_kernel(u64 const * __restrict__ src, u32 * __restrict__ dst, u64 const R64, u64 const C, u64 const dst_pitch32,
+	u32 const n_bands, u32 const n_tiles, unsigned *ticket)
+{
+	extern __shared__ __align__(16) u64 tile[];
+	__shared__ u32 s_next;
+	unsigned const tid(threadIdx.x);
+	[[maybe_unused]] u64 const st_policy(1 == V2M_K1_STORE_POLICY ? k1_policy_evict_last() : 0);
+	u32 const sbase(smem_u32(tile));
+	unsigned const q(tid & 7), lp(tid >> 3);					// load side: 64-bit word within the 64-byte piece, 32 lines per pass
+	unsigned const lane(tid & 31), qw(tid >> 5);				// transpose side: lane = line group, qw = pair of word columns
+	unsigned const rbase(256 * lane + 8 * (lane >> 3) + (qw ^ (lane & 7)));
+	u64 const C32(C / 32);
+
+	auto const issue([&](u32 const t) {
+		u64 const c0(u64(t / n_bands) * K1T_TC);
+		u64 const p0(u64(t % n_bands) * (K1T_TW / 2));
+		bool const pair_ok(p0 + q < R64);
+		u64 const *first(src + (c0 + lp) * R64 + p0 + q);
+		u64 const stride(32 * R64);
+		u32 const d0(sbase + 8 * (lp * 8));
+#pragma unroll
+		for (int p = 0; p < K1T_TC / 32; ++p)
+		{
+			bool const ok(pair_ok && c0 + 32 * p + lp < C);
+			u64 const *g(ok ? first + u64(p) * stride : src);
+			u32 const n(ok ? 8u : 0u);
+			u32 const d(d0 + 8 * (32 * p * 8 + 8 * (p >> 3)) + 8 * (q ^ (p & 7)));
+			asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;" :: "r"(d), "l"(g), "r"(n) : "memory");
+		}
+		asm volatile("cp.async.commit_group;" ::: "memory");
+	});
+
+	u32 const total(n_bands * n_tiles);
+	if (0 == tid) s_next = atomicAdd(ticket, 1u);
+	__syncthreads();
+	u32 t(s_next);
+	__syncthreads();
+	if (t < total && !(MODE & 2)) issue(t);
+	while (t < total)
+	{
+		if (0 == tid) s_next = atomicAdd(ticket, 1u);
+		asm volatile("cp.async.wait_group 0;" ::: "memory");
+		__syncthreads();
+		u32 const next(s_next);
+		u32 a[32], b[32];
+#pragma unroll
+		for (int i = 0; i < 32; ++i)
+		{
+			u64 const v(tile[rbase + 8 * i]);
+			a[i] = u32(v); b[i] = u32(v >> 32);
+		}
+		__syncthreads();
+		if (next < total && !(MODE & 2)) issue(next);
+		transpose32(a);
+		transpose32(b);
+
+		u64 const xw(u64(t / n_bands) * (K1T_TC / 32) + lane);
+		u64 const r0(64 * u64(t % n_bands) * (K1T_TW / 2) + 64 * qw);
+		if (xw < C32 && r0 < 64 * R64)							// rows are a multiple of 64: both sub-tiles or neither
+		{
+			u32 *out(dst + r0 * dst_pitch32 + xw);
+#pragma unroll
+			for (int j = 0; j < 32; ++j)
+				if (!(MODE & 1) || 0x12345678u == a[j]) k1_store(out + u64(j) * dst_pitch32, a[j], st_policy);
+			out += 32 * dst_pitch32;
+#pragma unroll
+			for (int j = 0; j < 32; ++j)
+				if (!(MODE & 1) || 0x12345678u == b[j]) k1_store(out + u64(j) * dst_pitch32, b[j], st_policy);
+		}
+		t = next;
+	}
+}
+
+
+// The wide form: tiles of 2048 source lines × 256 rows, 256 threads, every thread transposes TWO sub-tiles that lie side by
+// side along the destination lines (source lines 64 · lane … + 31 and … + 32 … + 63, word column = warp), so that it holds 8
+// consecutive bytes of each of its 32 destination lines and a warp's store is one 256-byte run of one line, 8 bytes per lane,
+// with no exchange between lanes. Why: the store shape is what bounds the tile kernels (profiles/r02_k1_patterns.txt — the L2
+// takes 64-byte runs of 4-byte pieces at 2.0 – 2.4 TB/s when lines start mid-sector, 256-byte runs of 8-byte pieces at 3.9 –
+// 4.3 TB/s, and a run's two partial sectors weigh 2 in 9 instead of 2 in 3), and the shear that removes the partial sectors
+// altogether costs more integer work than it saves (above). The price is on the read side: a tile takes 32-byte pieces of the
+// source lines (4 words), which straddle two sectors three times out of four; the neighbouring row band's CTA reads the other
+// halves at the same time (row bands vary fastest in the grid), so they come out of the L2.
+// Shared layout in 32-bit words: word c of line l at l · 8 + 8 · (l >> 6) + (c ^ ((l >> 8) & 7)) — the 32 lanes of a
+// transposing read (lines 64 · lane + i, one word column) hit banks 8 · (lane & 3) + (c ^ (lane >> 2)): all distinct.
+constexpr int K1W_LINES = 2048;
+constexpr int K1W_ROWS = 256;								// 4 64-bit words of every source line
+constexpr int K1W_THREADS = 256;
+constexpr int K1W_TILE_WORDS = K1W_LINES * 8 + 8 * (K1W_LINES / 64);
+constexpr int K1W_SMEM = K1W_TILE_WORDS * 4;
+
+__global__ void __launch_bounds__(K1W_THREADS, 2)
+transpose_bits_wide_kernel(u64 const * __restrict__ src, u32 * __restrict__ dst, u64 const R64, u64 const C, u64 const dst_pitch32)
+{
+	extern __shared__ __align__(16) u64 tile[];
+	u64 const c0(u64(blockIdx.y) * K1W_LINES);
+	u64 const p0(u64(blockIdx.x) * (K1W_ROWS / 64));			// first 64-bit word of the row band
+	unsigned const tid(threadIdx.x);
+	[[maybe_unused]] u64 const st_policy(1 == V2M_K1_STORE_POLICY ? k1_policy_evict_last() : 0);
+
+	// ---- load: 4 lanes per 32-byte piece, 64 lines per pass ----------------------------------------------------------------
+	{
+		unsigned const q(tid & 3), lp(tid >> 2);
+		bool const pair_ok(p0 + q < R64);
+		u64 const *first(src + (c0 + lp) * R64 + p0 + q);
+		u64 const stride(64 * R64);
+#pragma unroll
+		for (int half = 0; half < 2; ++half)
+		{
+			u64 vals[K1W_LINES / 128];
+#pragma unroll
+			for (int p = 0; p < K1W_LINES / 128; ++p)
+			{
+				int const pass(half * (K1W_LINES / 128) + p);
+				vals[p] = (pair_ok && c0 + 64 * pass + lp < C) ? __ldg(first + u64(pass) * stride) : 0;
+			}
+#pragma unroll
+			for (int p = 0; p < K1W_LINES / 128; ++p)
+			{
+				int const pass(half * (K1W_LINES / 128) + p);
+				unsigned const l(64 * pass + lp);
+				unsigned const sw((l >> 8) & 7);				// = (pass >> 2) & 7: known at compile time
+				u64 const v(vals[p]);
+				tile[l * 4 + 4 * pass + (q ^ (sw >> 1))] = (sw & 1) ? (v >> 32 | v << 32) : v;
+			}
+		}
+	}
+	__syncthreads();
+
+	// ---- two 32 × 32 sub-tiles per thread ---------------------------------------------------------------------------------------
+	unsigned const lane(tid & 31), yw(tid >> 5);					// lane = 64 source lines, yw = word column (32 rows)
+	u32 const *tile32(reinterpret_cast<u32 const *>(tile));
+	u32 a[32], b[32];
+	{
+		unsigned const base(520 * lane + (yw ^ ((lane >> 2) & 7)));
+#pragma unroll
+		for (int i = 0; i < 32; ++i) a[i] = tile32[base + 8 * i];
+#pragma unroll
+		for (int i = 0; i < 32; ++i) b[i] = tile32[base + 256 + 8 * i];
+	}
+	transpose32(a);
+	transpose32(b);
+
+	// ---- store: 8 bytes per lane, 256 bytes of one destination line per warp -------------------------------------------------------
+	u64 const C32(C / 32);
+	u64 const xw(c0 / 32 + 2 * lane);								// C is a multiple of 64: a pair of words is inside the line or not
+	u64 const r0(64 * p0 + 32 * yw);
+	if (xw < C32 && r0 < 64 * R64)
+	{
+		u32 *out(dst + r0 * dst_pitch32 + xw);
+#pragma unroll
+		for (int j = 0; j < 32; ++j)
+		{
+			u32 *const p(out + u64(j) * dst_pitch32);
+#if V2M_K1_STORE_POLICY == 1
+			asm volatile("st.global.L2::cache_hint.v2.b32 [%0], {%1, %2}, %3;" :: "l"(p), "r"(a[j]), "r"(b[j]), "l"(st_policy) : "memory");
+#else
+			asm volatile("st.global.v2.b32 [%0], {%1, %2};" :: "l"(p), "r"(a[j]), "r"(b[j]) : "memory");
+#endif
+		}
+	}
+}
+
+
+// Tile counters of the streaming kernels: a ring of 64 slots in device memory, one per launch in flight, zeroed on the launch's
+// stream before the kernel starts.
+static __device__ unsigned k1_ticket_ring[64];
+
+static int k1_ticket(unsigned **out, cudaStream_t stream)
+{
+	static std::atomic<unsigned> next{0};
+	void *base(nullptr);
+	V2M_CUDA_TRY(cudaGetSymbolAddress(&base, k1_ticket_ring));
+	unsigned *const slot(static_cast<unsigned *>(base) + next.fetch_add(1, std::memory_order_relaxed) % 64);
+	V2M_CUDA_TRY(cudaMemsetAsync(slot, 0, sizeof(unsigned), stream));
+	*out = slot;
+	return 0;
+}
+
 // dst_line_bits >= cols: the destination lines written are the first cols bits of lines that are dst_line_bits long (K5 fills
 // paths_by_chrom_copy_and_edge a range of edge columns at a time; d_dst then points at the range's first word of line 0).
 int launch_transpose_bits_into(void const *d_src, u64 rows, u64 cols, void *d_dst, u64 dst_line_bits, cudaStream_t stream)
@@ -382,7 +663,10 @@ int launch_transpose_bits_into(void const *d_src, u64 rows, u64 cols, void *d_ds
 	if (0 == cols || 0 == rows) return 0;
 	u64 const R64(rows / 64);
 	u64 const dst_pitch32(dst_line_bits / 32);
-	int const force([] { char const *env(std::getenv("V2M_K1_TALL")); return env ? std::atoi(env) : -1; }());	// experiments and tests: 0 / 1 / 2 (2: the sheared kernel wherever its grid allows)
+	// Experiments and tests (V2M_K1_TALL): 0 tile kernel, 1 tall, 2 sheared, 3 wide, 6 half-size tiles, 8 streaming; otherwise the
+	// choice below. V2M_K1_MODE: the ablations of kernels 1, 6 and 8.
+	int const force([] { char const *env(std::getenv("V2M_K1_TALL")); return env ? std::atoi(env) : -1; }());
+	int const mode([] { char const *env(std::getenv("V2M_K1_MODE")); return env ? std::atoi(env) : 0; }());
 	{
 		// The path matrix as build_variant_graph hands it over (rows = chromosome copies, one source line per edge) and anything
 		// of that kind: at least two full row bands and enough lines for the halo not to matter.
@@ -402,16 +686,65 @@ int launch_transpose_bits_into(void const *d_src, u64 rows, u64 cols, void *d_ds
 			return 0;
 		}
 	}
-	bool const tall(force >= 0 ? 1 == force : (rows <= 512 || 0 != (cols / 8) % 16));
+	if (8 == force)
+	{
+		u64 const n_bands((R64 + K1T_TW / 2 - 1) / (K1T_TW / 2)), n_tiles((cols + K1T_TC - 1) / K1T_TC);
+		if (n_bands * n_tiles > 0xffffffffull) return fail(1, "transpose_bits: too many tiles in one launch");
+		int dev(0), sms(0);
+		V2M_CUDA_TRY(cudaGetDevice(&dev));
+		V2M_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+		unsigned const ctas(unsigned(std::min<u64>(n_bands * n_tiles, u64(2) * sms)));
+		unsigned *ticket(nullptr);
+		if (int const rc = k1_ticket(&ticket, stream)) return rc;
+		auto const launch([&](auto kernel) -> int {
+			V2M_CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, K1P_SMEM));
+			kernel<<<ctas, K1P_THREADS, K1P_SMEM, stream>>>(static_cast<u64 const *>(d_src), static_cast<u32 *>(d_dst), R64, cols, dst_pitch32, u32(n_bands), u32(n_tiles), ticket);
+			V2M_CHECK_LAUNCH("transpose_bits_tall_pairs_kernel");
+			return 0;
+		});
+		return 1 == mode ? launch(transpose_bits_tall_pairs_kernel<1>) : 2 == mode ? launch(transpose_bits_tall_pairs_kernel<2>) : 3 == mode ? launch(transpose_bits_tall_pairs_kernel<3>) : launch(transpose_bits_tall_pairs_kernel<0>);
+	}
+	if (6 == force)
+	{
+		dim3 const grid(unsigned((R64 + K1S_TW / 2 - 1) / (K1S_TW / 2)), unsigned((cols + K1S_TC - 1) / K1S_TC));
+		if (grid.y > 65535u) return fail(1, "transpose_bits: too many source lines in one launch");
+		auto const launch([&](auto kernel) -> int {
+			V2M_CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, K1S_SMEM));
+			kernel<<<grid, K1S_THREADS, K1S_SMEM, stream>>>(static_cast<u64 const *>(d_src), static_cast<u32 *>(d_dst), R64, cols, dst_pitch32);
+			V2M_CHECK_LAUNCH("transpose_bits_small_kernel");
+			return 0;
+		});
+		return 1 == mode ? launch(transpose_bits_small_kernel<1>) : 2 == mode ? launch(transpose_bits_small_kernel<2>) : 3 == mode ? launch(transpose_bits_small_kernel<3>) : launch(transpose_bits_small_kernel<0>);
+	}
+	// The choice. Destination lines whose length is a multiple of 16 bytes (c5: 750,000) take the 512 × 1024 tile kernel; others —
+	// the path matrices of c4 (787,560-byte lines) and c2 (144,376), and the way back from copy-major to edge-major lines (632
+	// bytes) — the wide kernel when there are enough rows to fill its 256-row bands, else the tall one
+	// (profiles/r02_k1_variants.txt: c4 1.78 → 1.73 – 1.75 ms, c2 0.336 – 0.351 → 0.327 – 0.340, c4 back 3.50 – 3.64 → 2.58).
+	bool const misaligned(0 != (cols / 8) % 16);
+	bool const wide_ok(0 == dst_line_bits % 64 && 0 == reinterpret_cast<u64>(d_dst) % 8);
+	bool const wide(wide_ok && (force >= 0 ? 3 == force : (misaligned && rows > 512)));
+	if (wide)
+	{
+		dim3 const grid(unsigned((R64 + K1W_ROWS / 64 - 1) / (K1W_ROWS / 64)), unsigned((cols + K1W_LINES - 1) / K1W_LINES));
+		if (grid.y > 65535u) return fail(1, "transpose_bits: too many source lines in one launch");
+		V2M_CUDA_TRY(cudaFuncSetAttribute(transpose_bits_wide_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, K1W_SMEM));
+		transpose_bits_wide_kernel<<<grid, K1W_THREADS, K1W_SMEM, stream>>>(static_cast<u64 const *>(d_src), static_cast<u32 *>(d_dst), R64, cols, dst_pitch32);
+		V2M_CHECK_LAUNCH("transpose_bits_wide_kernel");
+		return 0;
+	}
+	bool const tall(force >= 0 ? 1 == force : (rows <= 512 || misaligned));
 	if (tall)
 	{
 		dim3 const grid(unsigned((R64 + K1T_TW / 2 - 1) / (K1T_TW / 2)), unsigned((cols + K1T_TC - 1) / K1T_TC));
 		if (grid.y > 65535u) return fail(1, "transpose_bits: too many source lines in one launch");
 		constexpr int smem_bytes((K1T_TC * K1T_TW + 16) * sizeof(u32));
-		V2M_CUDA_TRY(cudaFuncSetAttribute(transpose_bits_tall_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
-		transpose_bits_tall_kernel<<<grid, K1_THREADS, smem_bytes, stream>>>(static_cast<u64 const *>(d_src), static_cast<u32 *>(d_dst), R64, cols, dst_pitch32);
-		V2M_CHECK_LAUNCH("transpose_bits_tall_kernel");
-		return 0;
+		auto const launch([&](auto kernel) -> int {
+			V2M_CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
+			kernel<<<grid, K1_THREADS, smem_bytes, stream>>>(static_cast<u64 const *>(d_src), static_cast<u32 *>(d_dst), R64, cols, dst_pitch32);
+			V2M_CHECK_LAUNCH("transpose_bits_tall_kernel");
+			return 0;
+		});
+		return 1 == mode ? launch(transpose_bits_tall_kernel<1>) : 2 == mode ? launch(transpose_bits_tall_kernel<2>) : 3 == mode ? launch(transpose_bits_tall_kernel<3>) : launch(transpose_bits_tall_kernel<0>);
 	}
 	dim3 const grid(unsigned((R64 + K1_TW / 2 - 1) / (K1_TW / 2)), unsigned((cols + K1_TC - 1) / K1_TC));
 	if (grid.y > 65535u) return fail(1, "transpose_bits: more than 33,553,920 source lines in one launch");
