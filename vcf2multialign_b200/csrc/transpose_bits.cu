@@ -454,6 +454,75 @@ transpose_bits_small_kernel(u64 const * __restrict__ src, u32 * __restrict__ dst
 }
 
 
+// The tall tile with bulk stores (V2M_K1_TALL=9): the transposed sub-tiles go back into the (by then dead) shared tile in
+// destination order — 128 bytes per destination line — and every thread hands one line's 128 bytes to the copy engine
+// (cp.async.bulk shared → global). Needs 16-byte aligned runs, i.e. destination lines that are a multiple of 16 bytes long
+// (c5: 750,000; not c4 / c2, whose odd lines start 8 bytes into a 16-byte unit). Per thread 32 STS with immediate offsets and
+// one bulk copy replace 32 STG with a 64-bit address each.
+// RESULT (profiles/r02_k1_ablation.txt): bit-exact, and slower — 1.84 ms on c5 against 1.62 (1.86 against 1.42 on the sector-
+// aligned shape): transposes + stores take the same 1.15 ms as with the tall kernel's STG (29.6 M bulk copies of 128 bytes do
+// not reach the L2 in a better shape than 128-byte runs of 4-byte stores), and the third barrier and the wait for the copy
+// engine to have read the tile lengthen every CTA's tail. Opt-in, as the record of the experiment.
+template <int MODE>
+__global__ void __launch_bounds__(K1_THREADS, 2)
+transpose_bits_tall_bulk_kernel(u64 const * __restrict__ src, u8 * __restrict__ dst, u64 const R64, u64 const C, u64 const dst_pitch_bytes)
+{
+	extern __shared__ __align__(128) u64 tile[];
+	u64 const c0(u64(blockIdx.y) * K1T_TC);
+	u64 const p0(u64(blockIdx.x) * (K1T_TW / 2));
+	unsigned const tid(threadIdx.x);
+	{
+		unsigned const q(tid & 7), l_in_pass(tid >> 3);
+		bool const pair_ok(p0 + q < R64);
+		u64 vals[K1T_TC / 64];
+#pragma unroll
+		for (int p = 0; p < K1T_TC / 64; ++p)
+		{
+			u64 const line(c0 + 64 * p + l_in_pass);
+			vals[p] = (MODE & 2) ? u64(tid) * 0x9e3779b97f4a7c15ull + p : (pair_ok && line < C) ? __ldg(src + line * R64 + p0 + q) : 0;
+		}
+#pragma unroll
+		for (int p = 0; p < K1T_TC / 64; ++p)
+		{
+			unsigned const l(64 * p + l_in_pass);
+			unsigned const sw((l >> 5) & 15);
+			u64 const v(vals[p]);
+			tile[l * 8 + 8 * (l >> 9) + (q ^ (sw >> 1))] = (sw & 1) ? (v >> 32 | v << 32) : v;
+		}
+	}
+	__syncthreads();
+
+	unsigned const lane(tid & 31), yw(tid >> 5);
+	u32 *tile32(reinterpret_cast<u32 *>(tile));
+	u32 a[32];
+	{
+		unsigned const base(32 * lane * 16 + 16 * (lane >> 4) + (yw ^ (lane & 15)));
+#pragma unroll
+		for (int i = 0; i < 32; ++i) a[i] = tile32[base + i * 16];
+	}
+	__syncthreads();											// the source tile is dead: its place takes the tile in destination order
+	transpose32(a);
+	{
+		u32 *stage(tile32 + (32 * yw) * 32 + lane);				// line 32 · yw + j of the band, word `lane` of its 128 bytes
+#pragma unroll
+		for (int j = 0; j < 32; ++j) stage[j * 32] = a[j];
+	}
+	fence_proxy_async_smem();
+	__syncthreads();
+
+	u64 const LB(C / 8);
+	u64 const x_bytes(u64(blockIdx.y) * (K1T_TC / 8));
+	u64 const row(64 * p0 + tid);
+	if (!(MODE & 1) && row < 64 * R64 && x_bytes < LB)
+	{
+		u32 const bytes(u32(min(u64(K1T_TC / 8), LB - x_bytes)));		// a multiple of 16: LB is
+		bulk_s2g(dst + row * dst_pitch_bytes + x_bytes, tile32 + tid * 32, bytes);
+	}
+	bulk_commit();
+	bulk_wait_read<0>();
+}
+
+
 // The tall tile as a stream (opt-in, V2M_K1_TALL=8; the record of an experiment): persistent CTAs, two per SM, draw tiles from
 // a counter, row bands fastest, and the source pieces of the next tile are on their way into shared memory (8-byte cp.async: no
 // registers, no waiting warps) while the current one is transposed and stored. One buffer is enough: the copies are issued
@@ -663,7 +732,7 @@ int launch_transpose_bits_into(void const *d_src, u64 rows, u64 cols, void *d_ds
 	if (0 == cols || 0 == rows) return 0;
 	u64 const R64(rows / 64);
 	u64 const dst_pitch32(dst_line_bits / 32);
-	// Experiments and tests (V2M_K1_TALL): 0 tile kernel, 1 tall, 2 sheared, 3 wide, 6 half-size tiles, 8 streaming; otherwise the
+	// Experiments and tests (V2M_K1_TALL): 0 tile kernel, 1 tall, 2 sheared, 3 wide, 6 half-size tiles, 8 streaming, 9 bulk stores; otherwise the
 	// choice below. V2M_K1_MODE: the ablations of kernels 1, 6 and 8.
 	int const force([] { char const *env(std::getenv("V2M_K1_TALL")); return env ? std::atoi(env) : -1; }());
 	int const mode([] { char const *env(std::getenv("V2M_K1_MODE")); return env ? std::atoi(env) : 0; }());
@@ -685,6 +754,19 @@ int launch_transpose_bits_into(void const *d_src, u64 rows, u64 cols, void *d_ds
 			V2M_CHECK_LAUNCH("transpose_bits_sheared_kernel");
 			return 0;
 		}
+	}
+	if (9 == force && 0 == (cols / 8) % 16 && 0 == (dst_line_bits / 8) % 16 && 0 == reinterpret_cast<u64>(d_dst) % 16)
+	{
+		dim3 const grid(unsigned((R64 + K1T_TW / 2 - 1) / (K1T_TW / 2)), unsigned((cols + K1T_TC - 1) / K1T_TC));
+		if (grid.y > 65535u) return fail(1, "transpose_bits: too many source lines in one launch");
+		constexpr int smem_bytes((K1T_TC * K1T_TW + 16) * sizeof(u32));
+		auto const launch([&](auto kernel) -> int {
+			V2M_CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
+			kernel<<<grid, K1_THREADS, smem_bytes, stream>>>(static_cast<u64 const *>(d_src), static_cast<u8 *>(d_dst), R64, cols, dst_line_bits / 8);
+			V2M_CHECK_LAUNCH("transpose_bits_tall_bulk_kernel");
+			return 0;
+		});
+		return 1 == mode ? launch(transpose_bits_tall_bulk_kernel<1>) : 2 == mode ? launch(transpose_bits_tall_bulk_kernel<2>) : 3 == mode ? launch(transpose_bits_tall_bulk_kernel<3>) : launch(transpose_bits_tall_bulk_kernel<0>);
 	}
 	if (8 == force)
 	{
