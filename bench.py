@@ -427,7 +427,9 @@ def main():
             t = C.c_float()
             check(L.v2m_cuda_time_transpose_bits(d_paths, g.h_pad, g.e_pad, d_scratch, 3, C.byref(t)))
             check(L.v2m_cuda_time_transpose_bits(d_paths, g.h_pad, g.e_pad, d_scratch, 10, C.byref(t)))
-            kernels["transpose_bits_kernel"] = {"shape": [int(g.h_pad), int(g.e_pad)], "ms": float(t.value), "gbs": 2 * path_bytes / (t.value * 1e-3) / 1e9,
+            # the launcher's choice for this shape (csrc/transpose_bits.cu): the wide kernel where destination lines are 8 mod 16 bytes long
+            k1_name = "transpose_bits_wide_kernel" if (g.e_pad // 8) % 16 and g.h_pad > 512 else "transpose_bits_tall_kernel" if g.h_pad <= 512 else "transpose_bits_kernel"
+            kernels[k1_name] = {"shape": [int(g.h_pad), int(g.e_pad)], "ms": float(t.value), "gbs": 2 * path_bytes / (t.value * 1e-3) / 1e9,
                                                 "frac": 2 * path_bytes / (t.value * 1e-3) / 1e9 / peak, "bytes": 2 * path_bytes,
                                                 "note": "K1 on this workload's path matrix (once per graph, outside the step); --workload c5 for the 5056 x 6,000,000 microbench"}
             L.v2m_cuda_device_free(d_scratch)
