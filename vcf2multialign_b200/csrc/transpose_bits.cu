@@ -38,7 +38,13 @@
 //           a persistent kernel with cp.async prefetch (1.65), two sub-tiles per thread with 8-byte stores in 256-byte runs (the
 //           wide kernel, 1.64; 2.86 when held to 3 CTAs per SM — the L1 that is left no longer covers the loads), ld.global.cg /
 //           L1::no_allocate / .lu / L2 evict-first loads (1.62 / 1.94 / 1.92 / 1.92). The wide kernel wins where destination lines
-//           are 8 mod 16 bytes long and is the launcher's choice there.
+//           are 8 mod 16 bytes long and is the launcher's choice there. Its own ablations: transposes 0.63 ms, + stores 0.82 (the
+//           256-byte runs cost next to nothing, on every shape), + loads 1.23 (its 32-byte source pieces straddle two sectors three
+//           times out of four; L2 → L1 traffic 10.5 GB for 3.79), everything 1.64. Loads and stores with the transposes left out
+//           take as long as the whole kernel for the 512-line tiles (1.61 ms on c5, 1.41 aligned): the integer work is hidden, the
+//           memory side of this tiling is the bound. A cluster of two CTAs that shares a 2048-line × 512-row tile through
+//           distributed shared memory (64-byte pieces AND 256-byte runs) was built and measured: bit-exact, 6.3 ms — 64 scalar
+//           ld.shared::cluster per thread alone take 5 ms; removed.
 //
 // Algorithmic bytes: 2 · R · C / 8 (each bit read once, written once). Roofline: HBM read + write.
 #include <algorithm>
@@ -207,7 +213,7 @@ transpose_bits_tall_kernel(u64 const * __restrict__ src, u32 * __restrict__ dst,
 		for (int i = 0; i < 32; ++i)
 			a[i] = tile32[base + i * 16];
 	}
-	transpose32(a);
+	if (!(MODE & 4)) transpose32(a);
 
 	u64 const C32(C / 32);
 	u64 const xw(c0 / 32 + lane);
@@ -397,7 +403,7 @@ constexpr int K1S_THREADS = 256;
 constexpr int K1S_SMEM = (K1S_TC * K1S_TW + 16 * (K1S_TC / 32)) * 4;
 
 // MODE (ablations for profiles/r02_k1_ablation.txt, V2M_K1_MODE): 0 the kernel; 1 no stores (kept alive by a test that never
-// holds); 2 no loads (the tile is made of thread indices); 3 neither.
+// holds); 2 no loads (the tile is made of thread indices); 3 neither; 4 loads and stores but no transposes (the memory side alone).
 template <bool EDGE, int MODE = 0>
 __device__ __forceinline__ void k1s_tile(u64 const * __restrict__ src, u32 * __restrict__ dst, u64 const R64, u64 const C, u64 const dst_pitch32, u64 *tile)
 {
@@ -430,7 +436,7 @@ __device__ __forceinline__ void k1s_tile(u64 const * __restrict__ src, u32 * __r
 #pragma unroll
 		for (int i = 0; i < 32; ++i) a[i] = tile32[base + 16 * i];
 	}
-	transpose32(a);
+	if (!(MODE & 4)) transpose32(a);
 
 	u64 const xw(c0 / 32 + xl);
 	u64 const r0(64 * p0 + 32 * yw);
@@ -467,7 +473,7 @@ template <int MODE>
 __global__ void __launch_bounds__(K1_THREADS, 2)
 transpose_bits_tall_bulk_kernel(u64 const * __restrict__ src, u8 * __restrict__ dst, u64 const R64, u64 const C, u64 const dst_pitch_bytes)
 {
-	extern __shared__ __align__(128) u64 tile[];
+	extern __shared__ __align__(16) u64 tile[];
 	u64 const c0(u64(blockIdx.y) * K1T_TC);
 	u64 const p0(u64(blockIdx.x) * (K1T_TW / 2));
 	unsigned const tid(threadIdx.x);
@@ -637,6 +643,7 @@ constexpr int K1W_THREADS = 256;
 constexpr int K1W_TILE_WORDS = K1W_LINES * 8 + 8 * (K1W_LINES / 64);
 constexpr int K1W_SMEM = K1W_TILE_WORDS * 4;
 
+template <int MODE>
 __global__ void __launch_bounds__(K1W_THREADS, 2)
 transpose_bits_wide_kernel(u64 const * __restrict__ src, u32 * __restrict__ dst, u64 const R64, u64 const C, u64 const dst_pitch32)
 {
@@ -660,7 +667,7 @@ transpose_bits_wide_kernel(u64 const * __restrict__ src, u32 * __restrict__ dst,
 			for (int p = 0; p < K1W_LINES / 128; ++p)
 			{
 				int const pass(half * (K1W_LINES / 128) + p);
-				vals[p] = (pair_ok && c0 + 64 * pass + lp < C) ? __ldg(first + u64(pass) * stride) : 0;
+				vals[p] = (MODE & 2) ? u64(tid) * 0x9e3779b97f4a7c15ull + p : (pair_ok && c0 + 64 * pass + lp < C) ? __ldg(first + u64(pass) * stride) : 0;
 			}
 #pragma unroll
 			for (int p = 0; p < K1W_LINES / 128; ++p)
@@ -686,8 +693,11 @@ transpose_bits_wide_kernel(u64 const * __restrict__ src, u32 * __restrict__ dst,
 #pragma unroll
 		for (int i = 0; i < 32; ++i) b[i] = tile32[base + 256 + 8 * i];
 	}
-	transpose32(a);
-	transpose32(b);
+	if (!(MODE & 4))
+	{
+		transpose32(a);
+		transpose32(b);
+	}
 
 	// ---- store: 8 bytes per lane, 256 bytes of one destination line per warp -------------------------------------------------------
 	u64 const C32(C / 32);
@@ -700,6 +710,7 @@ transpose_bits_wide_kernel(u64 const * __restrict__ src, u32 * __restrict__ dst,
 		for (int j = 0; j < 32; ++j)
 		{
 			u32 *const p(out + u64(j) * dst_pitch32);
+			if ((MODE & 1) && 0x12345678u != a[j]) continue;
 #if V2M_K1_STORE_POLICY == 1
 			asm volatile("st.global.L2::cache_hint.v2.b32 [%0], {%1, %2}, %3;" :: "l"(p), "r"(a[j]), "r"(b[j]), "l"(st_policy) : "memory");
 #else
@@ -733,7 +744,7 @@ int launch_transpose_bits_into(void const *d_src, u64 rows, u64 cols, void *d_ds
 	u64 const R64(rows / 64);
 	u64 const dst_pitch32(dst_line_bits / 32);
 	// Experiments and tests (V2M_K1_TALL): 0 tile kernel, 1 tall, 2 sheared, 3 wide, 6 half-size tiles, 8 streaming, 9 bulk stores; otherwise the
-	// choice below. V2M_K1_MODE: the ablations of kernels 1, 6 and 8.
+	// choice below. V2M_K1_MODE: the ablations of kernels 1, 3, 6, 8 and 9.
 	int const force([] { char const *env(std::getenv("V2M_K1_TALL")); return env ? std::atoi(env) : -1; }());
 	int const mode([] { char const *env(std::getenv("V2M_K1_MODE")); return env ? std::atoi(env) : 0; }());
 	{
@@ -796,7 +807,7 @@ int launch_transpose_bits_into(void const *d_src, u64 rows, u64 cols, void *d_ds
 			V2M_CHECK_LAUNCH("transpose_bits_small_kernel");
 			return 0;
 		});
-		return 1 == mode ? launch(transpose_bits_small_kernel<1>) : 2 == mode ? launch(transpose_bits_small_kernel<2>) : 3 == mode ? launch(transpose_bits_small_kernel<3>) : launch(transpose_bits_small_kernel<0>);
+		return 1 == mode ? launch(transpose_bits_small_kernel<1>) : 2 == mode ? launch(transpose_bits_small_kernel<2>) : 3 == mode ? launch(transpose_bits_small_kernel<3>) : 4 == mode ? launch(transpose_bits_small_kernel<4>) : launch(transpose_bits_small_kernel<0>);
 	}
 	// The choice. Destination lines whose length is a multiple of 16 bytes (c5: 750,000) take the 512 × 1024 tile kernel; others —
 	// the path matrices of c4 (787,560-byte lines) and c2 (144,376), and the way back from copy-major to edge-major lines (632
@@ -809,10 +820,13 @@ int launch_transpose_bits_into(void const *d_src, u64 rows, u64 cols, void *d_ds
 	{
 		dim3 const grid(unsigned((R64 + K1W_ROWS / 64 - 1) / (K1W_ROWS / 64)), unsigned((cols + K1W_LINES - 1) / K1W_LINES));
 		if (grid.y > 65535u) return fail(1, "transpose_bits: too many source lines in one launch");
-		V2M_CUDA_TRY(cudaFuncSetAttribute(transpose_bits_wide_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, K1W_SMEM));
-		transpose_bits_wide_kernel<<<grid, K1W_THREADS, K1W_SMEM, stream>>>(static_cast<u64 const *>(d_src), static_cast<u32 *>(d_dst), R64, cols, dst_pitch32);
-		V2M_CHECK_LAUNCH("transpose_bits_wide_kernel");
-		return 0;
+		auto const launch([&](auto kernel) -> int {
+			V2M_CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, K1W_SMEM));
+			kernel<<<grid, K1W_THREADS, K1W_SMEM, stream>>>(static_cast<u64 const *>(d_src), static_cast<u32 *>(d_dst), R64, cols, dst_pitch32);
+			V2M_CHECK_LAUNCH("transpose_bits_wide_kernel");
+			return 0;
+		});
+		return 1 == mode ? launch(transpose_bits_wide_kernel<1>) : 2 == mode ? launch(transpose_bits_wide_kernel<2>) : 3 == mode ? launch(transpose_bits_wide_kernel<3>) : 4 == mode ? launch(transpose_bits_wide_kernel<4>) : launch(transpose_bits_wide_kernel<0>);
 	}
 	bool const tall(force >= 0 ? 1 == force : (rows <= 512 || misaligned));
 	if (tall)
@@ -826,7 +840,7 @@ int launch_transpose_bits_into(void const *d_src, u64 rows, u64 cols, void *d_ds
 			V2M_CHECK_LAUNCH("transpose_bits_tall_kernel");
 			return 0;
 		});
-		return 1 == mode ? launch(transpose_bits_tall_kernel<1>) : 2 == mode ? launch(transpose_bits_tall_kernel<2>) : 3 == mode ? launch(transpose_bits_tall_kernel<3>) : launch(transpose_bits_tall_kernel<0>);
+		return 1 == mode ? launch(transpose_bits_tall_kernel<1>) : 2 == mode ? launch(transpose_bits_tall_kernel<2>) : 3 == mode ? launch(transpose_bits_tall_kernel<3>) : 4 == mode ? launch(transpose_bits_tall_kernel<4>) : launch(transpose_bits_tall_kernel<0>);
 	}
 	dim3 const grid(unsigned((R64 + K1_TW / 2 - 1) / (K1_TW / 2)), unsigned((cols + K1_TC - 1) / K1_TC));
 	if (grid.y > 65535u) return fail(1, "transpose_bits: more than 33,553,920 source lines in one launch");
