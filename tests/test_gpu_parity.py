@@ -77,10 +77,10 @@ def test_transpose_more_shapes(v2m, rows, cols):
 
 @pytest.mark.parametrize("rows,cols", [(1024, 8192), (1088, 3264), (576, 5184), (64, 1024), (512, 64), (5056, 11328), (1280, 20480 + 448), (2112, 1024 * 7 + 64),
                                        (640, 1024 * 33 + 8 * 64 * 3), (1216, 1024 * 5 + 192)])
-@pytest.mark.parametrize("kernel", ["2", "0", "1", "3", "6", "8", "9"])
+@pytest.mark.parametrize("kernel", ["2", "0", "1", "3", "6", "8", "9", "12"])
 def test_transpose_every_kernel_on_ragged_shapes(v2m, monkeypatch, rows, cols, kernel):
     """Every K1 kernel (V2M_K1_TALL = 0: 512 x 1024 tiles, 1: tall tiles, 2: sheared, 3: wide with two sub-tiles per thread,
-    6: half-size tiles, 8: persistent streaming kernel with cp.async, 9: bulk stores where lines allow them) on shapes with short last bands / last tiles and destination
+    6: half-size tiles, 8: persistent streaming kernel with cp.async, 9: bulk stores where lines allow them, 12: 1024 x 256 tiles) on shapes with short last bands / last tiles and destination
     lines at every 8-byte phase of a 32-byte sector."""
     monkeypatch.setenv("V2M_K1_TALL", kernel)
     rng = np.random.default_rng(rows * 7 + cols)

@@ -626,6 +626,76 @@ transpose_bits_tall_pairs_kernel(u64 const * __restrict__ src, u32 * __restrict_
 }
 
 
+// Quarter-height tall tiles (V2M_K1_TALL=12): 1024 source lines × 256 rows (32-byte source pieces), 256 threads, one sub-tile per
+// thread, 4 CTAs per SM — the tall kernel's stores (lane = line group: 128 bytes of one destination line per warp store) at the
+// occupancy at which the half-size-tile kernel's loads cost next to nothing. Separates the two things the wide kernel's loads
+// could be suffering from: the 32-byte pieces or the 16 warps per SM.
+// RESULT (profiles/r02_k1_ablation.txt): 1.575 ms on c5, 1.73 on c4, 1.59 aligned, 0.327 on c2 — the best of all kernels on c5
+// and c4 by 1 – 2 %, which is nothing; opt-in. Transposes 0.75 ms, with loads 1.03, with stores 0.98, loads + stores without the
+// transposes 1.51: reads and writes do not overlap in DRAM time, and that sum is what every kernel in this file ends up at.
+// Shared layout in 32-bit words: word c of line l at l · 8 + 8 · (l >> 8) + (c ^ ((l >> 5) & 7)).
+constexpr int K1Q_TC = 1024;
+constexpr int K1Q_THREADS = 256;
+constexpr int K1Q_SMEM = (K1Q_TC * 8 + 8 * (K1Q_TC / 256)) * 4;
+
+template <bool EDGE, int MODE>
+__device__ __forceinline__ void k1q_tile(u64 const * __restrict__ src, u32 * __restrict__ dst, u64 const R64, u64 const C, u64 const dst_pitch32, u64 *tile)
+{
+	u64 const c0(u64(blockIdx.y) * K1Q_TC);
+	u64 const p0(u64(blockIdx.x) * 4);
+	unsigned const tid(threadIdx.x);
+	[[maybe_unused]] u64 const st_policy(1 == V2M_K1_STORE_POLICY ? k1_policy_evict_last() : 0);
+	{
+		unsigned const q(tid & 3), lp(tid >> 2);					// 64 lines per pass
+		u64 const *first(src + (c0 + lp) * R64 + p0 + q);
+		u64 const stride(64 * R64);
+		[[maybe_unused]] bool const pair_ok(p0 + q < R64);
+		bool const swap(0 != ((lp >> 5) & 1));						// (l >> 5) & 1
+		u64 vals[K1Q_TC / 64];
+#pragma unroll
+		for (int p = 0; p < K1Q_TC / 64; ++p)
+			vals[p] = (MODE & 2) ? u64(tid) * 0x9e3779b97f4a7c15ull + p : (!EDGE || (pair_ok && c0 + 64 * p + lp < C)) ? __ldg(first + u64(p) * stride) : 0;
+#pragma unroll
+		for (int p = 0; p < K1Q_TC / 64; ++p)
+		{
+			u64 const v(vals[p]);
+			tile[(64 * p + lp) * 4 + 4 * (p >> 2) + (q ^ (p & 3))] = swap ? (v >> 32 | v << 32) : v;
+		}
+	}
+	__syncthreads();
+
+	unsigned const lane(tid & 31), w(tid >> 5);
+	u32 const *tile32(reinterpret_cast<u32 const *>(tile));
+	u32 a[32];
+	{
+		unsigned const base(256 * lane + 8 * (lane >> 3) + (w ^ (lane & 7)));
+#pragma unroll
+		for (int i = 0; i < 32; ++i) a[i] = tile32[base + 8 * i];
+	}
+	if (!(MODE & 4)) transpose32(a);
+
+	u64 const xw(c0 / 32 + lane);
+	u64 const r0(64 * p0 + 32 * w);
+	if (!EDGE || (xw < C / 32 && r0 < 64 * R64))
+	{
+		u32 *out(dst + r0 * dst_pitch32 + xw);
+#pragma unroll
+		for (int j = 0; j < 32; ++j)
+			if (!(MODE & 1) || 0x12345678u == a[j]) k1_store(out + u64(j) * dst_pitch32, a[j], st_policy);
+	}
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(K1Q_THREADS, 4)
+transpose_bits_quarter_kernel(u64 const * __restrict__ src, u32 * __restrict__ dst, u64 const R64, u64 const C, u64 const dst_pitch32)
+{
+	extern __shared__ __align__(16) u64 tile[];
+	bool const edge((u64(blockIdx.y) + 1) * K1Q_TC > C || (u64(blockIdx.x) + 1) * 4 > R64);
+	if (edge) k1q_tile<true, MODE>(src, dst, R64, C, dst_pitch32, tile);
+	else k1q_tile<false, MODE>(src, dst, R64, C, dst_pitch32, tile);
+}
+
+
 // The wide form: tiles of 2048 source lines × 256 rows, 256 threads, every thread transposes TWO sub-tiles that lie side by
 // side along the destination lines (source lines 64 · lane … + 31 and … + 32 … + 63, word column = warp), so that it holds 8
 // consecutive bytes of each of its 32 destination lines and a warp's store is one 256-byte run of one line, 8 bytes per lane,
@@ -743,7 +813,7 @@ int launch_transpose_bits_into(void const *d_src, u64 rows, u64 cols, void *d_ds
 	if (0 == cols || 0 == rows) return 0;
 	u64 const R64(rows / 64);
 	u64 const dst_pitch32(dst_line_bits / 32);
-	// Experiments and tests (V2M_K1_TALL): 0 tile kernel, 1 tall, 2 sheared, 3 wide, 6 half-size tiles, 8 streaming, 9 bulk stores; otherwise the
+	// Experiments and tests (V2M_K1_TALL): 0 tile kernel, 1 tall, 2 sheared, 3 wide, 6 half-size tiles, 8 streaming, 9 bulk stores, 12 quarter-height tall tiles; otherwise the
 	// choice below. V2M_K1_MODE: the ablations of kernels 1, 3, 6, 8 and 9.
 	int const force([] { char const *env(std::getenv("V2M_K1_TALL")); return env ? std::atoi(env) : -1; }());
 	int const mode([] { char const *env(std::getenv("V2M_K1_MODE")); return env ? std::atoi(env) : 0; }());
@@ -778,6 +848,18 @@ int launch_transpose_bits_into(void const *d_src, u64 rows, u64 cols, void *d_ds
 			return 0;
 		});
 		return 1 == mode ? launch(transpose_bits_tall_bulk_kernel<1>) : 2 == mode ? launch(transpose_bits_tall_bulk_kernel<2>) : 3 == mode ? launch(transpose_bits_tall_bulk_kernel<3>) : launch(transpose_bits_tall_bulk_kernel<0>);
+	}
+	if (12 == force)
+	{
+		dim3 const grid(unsigned((R64 + 3) / 4), unsigned((cols + K1Q_TC - 1) / K1Q_TC));
+		if (grid.y > 65535u) return fail(1, "transpose_bits: too many source lines in one launch");
+		auto const launch([&](auto kernel) -> int {
+			V2M_CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, K1Q_SMEM));
+			kernel<<<grid, K1Q_THREADS, K1Q_SMEM, stream>>>(static_cast<u64 const *>(d_src), static_cast<u32 *>(d_dst), R64, cols, dst_pitch32);
+			V2M_CHECK_LAUNCH("transpose_bits_quarter_kernel");
+			return 0;
+		});
+		return 1 == mode ? launch(transpose_bits_quarter_kernel<1>) : 2 == mode ? launch(transpose_bits_quarter_kernel<2>) : 3 == mode ? launch(transpose_bits_quarter_kernel<3>) : 4 == mode ? launch(transpose_bits_quarter_kernel<4>) : launch(transpose_bits_quarter_kernel<0>);
 	}
 	if (8 == force)
 	{
