@@ -271,6 +271,8 @@ int v2m_cuda_paths_from_genotypes_both(const uint16_t *gt, uint64_t n_records, u
  * LIMIT: n_copies <= V2M_NO_ALLOC_MAX_COPIES, else V2M_ERR_ARGUMENT (use v2m_cuda_paths_from_genotypes_device).
  * The array is shared by every call on a GPU and keeps the last call's contents (the part a call uses is cleared on `stream`
  * first): calls that overlap on one GPU — two host threads, or two streams — race; serialise them.
+ * The first call on a device looks the array's device address up (cudaGetSymbolAddress) and, under CUDA's lazy module loading,
+ * loads the kernels: make one warm-up call per device before entering a region where that is not allowed.
  * Work is enqueued on `stream` (NULL = the default stream); the call returns after the stream has drained, with
  * V2M_ERR_ARGUMENT for a genotype naming an ALT its record does not have, or when more than overlap_cap pairs were found
  * (needed count in *n_overlaps; the first overlap_cap pairs are valid). */
